@@ -1,0 +1,154 @@
+/* ptb.h - C ABI of the B200-native path-tracing hot path (libptb.so).
+ *
+ * Drop-in boundary for thiagoald/pathtracerpython's per-pixel, per-sample radiance estimation.
+ * The reference has no FFI; its seams are plain Python calls.  Each entry point below names the
+ * reference interface it replaces (file:line under the reference tree).  Host code binds these with
+ * ctypes (pathtracerpython_b200/_lib.py); INTEGRATION.md shows the stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * ptb_status, with text available from ptb_last_error(); no exceptions or callbacks cross the
+ * boundary; pointers named d_* are DEVICE pointers owned by the caller (the Python host allocates
+ * them as torch tensors), pointers named h_* / inside ptb_scene_desc are HOST pointers; every
+ * launch goes to the caller's CUDA stream (a cudaStream_t passed as void*).  A scene handle is
+ * immutable after creation and bound to the device that was current when it was created.
+ */
+#ifndef PTB_H
+#define PTB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PTB_OK = 0,
+    PTB_ERR_ARG = -1,      /* bad argument */
+    PTB_ERR_CUDA = -2,     /* CUDA runtime error (text in ptb_last_error) */
+    PTB_ERR_NOMEM = -3,    /* workspace too small */
+    PTB_ERR_UNSUPPORTED = -4
+} ptb_status;
+
+/* Flattened scene = the data the reference keeps in `Scene` / `Obj` objects
+ * (scene_reader.py:49-60, 82-88, 108-121, 171-183).  Triangles are listed in the order
+ * intersect_objects visits them (main.py:91-96): every `object` in file order, the light mesh last. */
+typedef struct {
+    int32_t n_tri;              /* closest-hit set: object triangles + light triangles (main.py:91) */
+    int32_t n_tri_obj;          /* occlusion set: object triangles only (main.py:42) */
+    int32_t n_obj;              /* len(scene.objects); light triangles carry object index n_obj */
+    int32_t n_light_tri;        /* == n_tri - n_tri_obj */
+    const double *verts;        /* [n_tri][3][3]  Obj.triangles   (scene_reader.py:83-86) */
+    const double *normals;      /* [n_tri][3]     Obj.normals     (scene_reader.py:5-8, 87) */
+    const int32_t *tri_obj;     /* [n_tri]        index into scene.objects */
+    const double *mat;          /* [n_obj][8]     red green blue ka kd ks kt n (scene_reader.py:175-182) */
+    const double *light_areas;  /* [n_light_tri]  light_obj.areas (scene_reader.py:88) */
+    double eye[3];              /* scene.eye      (scene_reader.py:152) */
+    double ortho[4];            /* scene.ortho x0 y0 x1 y1 (scene_reader.py:157) */
+    double ambient;             /* scene.ambient  (scene_reader.py:161) */
+    double light_color[3];      /* scene.light_color[:3] (scene_reader.py:164) */
+    int32_t accel;              /* PTB_ACCEL_* */
+    int32_t reserved;
+} ptb_scene_desc;
+
+enum { PTB_ACCEL_AUTO = 0, PTB_ACCEL_BRUTE = 1, PTB_ACCEL_LBVH = 2 };
+
+typedef struct ptb_scene ptb_scene;
+
+/* Which pixels a call renders.  Ray index r = ix*H + iy (utils.py:64-69).  With d_pixels == NULL the
+ * call covers the shard { r in [0, W*H) : (r / tile) % n_shards == shard } (tile-interleaved sharding
+ * for multi-GPU; n_shards = 1 covers the frame).  With d_pixels != NULL it covers that explicit list
+ * of n_pixels ray indices (device int32). */
+typedef struct {
+    int32_t width, height;      /* scene.width / scene.height (scene_reader.py:154-155) */
+    int32_t shard, n_shards, tile;
+    int32_t n_pixels;           /* only with d_pixels */
+    const int32_t *d_pixels;
+} ptb_pixels;
+
+enum { PTB_PREC_FP32 = 0, PTB_PREC_FP64 = 1 };
+enum {
+    PTB_FLAG_NO_FP64_RETRACE = 1,   /* FP32 only: skip the FP64 re-trace of uncertain primary hits */
+    PTB_FLAG_SHARE_PRIMARY = 2      /* trace the (identical, main.py:191) primary ray once per pixel */
+};
+
+typedef struct {
+    ptb_pixels px;
+    int32_t sample_begin, sample_end;   /* samples [s0, s1)  = main.py:186 `rays_counter`, -r */
+    int32_t bounces;                    /* main.py:192, -b */
+    uint32_t seed;                      /* Philox key (the reference's RNG is unseeded, A-Q18) */
+    int32_t precision;                  /* PTB_PREC_* */
+    int32_t flags;                      /* PTB_FLAG_* */
+    int32_t samples_per_batch;          /* 0 = choose from the workspace size */
+    int32_t reserved;
+} ptb_render_params;
+
+/* Optional per-(pixel, sample, bounce) records for parity check 2; all device pointers, any may be
+ * NULL.  Index = ((pixel_slot * n_samples) + (sample - sample_begin)) * bounces + bounce, where
+ * pixel_slot is the position of the pixel in the call's pixel set. */
+typedef struct {
+    int32_t *d_tri;        /* closest-hit triangle id, -1 miss, -2 path already ended */
+    float *d_contrib;      /* [..][3] new_color * accumulated_k (main.py:230-231) */
+    float *d_k_after;      /* accumulated_k after the bounce (main.py:251, 263) */
+    int8_t *d_lobe;        /* 0 diffuse, 1 specular, -1 none (main.py:241) */
+    int8_t *d_occ;         /* bit s set = light sample s occluded (main.py:49-51) */
+    int8_t *d_leak;        /* object index the NEE colour is taken from (main.py:42, 70) */
+    double *d_contrib64;   /* FP64 mode: same as d_contrib in double */
+    double *d_k_after64;
+} ptb_path_records;
+
+typedef struct {
+    uint64_t closest_rays;   /* closest-hit rays traced (intersect_objects calls on live paths) */
+    uint64_t shadow_rays;    /* shadow rays traced (3 per compute_color call) */
+    uint64_t shaded;         /* compute_color calls */
+    uint64_t samples;        /* pixel samples started */
+    uint64_t retraced;       /* primary rays re-traced in FP64 */
+    uint64_t launches;       /* kernels launched by this library since ptb_counters_reset */
+    uint64_t nodes_visited;  /* instrumented builds only */
+    uint64_t tris_tested;
+} ptb_counters;
+
+const char *ptb_last_error(void);
+int ptb_version(void);
+
+/* replaces Scene(path) object hand-off into main() (main.py:167) + the per-task pickling of the
+ * scene (main.py:199-201): uploads the flattened scene and builds the acceleration structure. */
+int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out);
+int ptb_scene_destroy(ptb_scene *scene);
+int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, double *build_ms);
+
+/* replaces make_screen_pts + make_rays + one round of intersect_objects over all primary rays
+ * (utils.py:55-69, main.py:191, 199-204, 83-122).  d_tri[i]: global triangle id or -1; d_t[i]:
+ * signed ray parameter of the hit (unit direction) or 0.  n outputs = size of the pixel set. */
+int ptb_trace_primary(const ptb_scene *scene, const ptb_pixels *px, int32_t precision, int32_t flags,
+                      int32_t *d_tri, float *d_t, void *d_workspace, size_t workspace_bytes, void *stream);
+
+/* closest hit for caller-supplied rays (intersect_objects, main.py:83-122): d_rays [n][6] (origin,
+ * direction; float for FP32, double for FP64). */
+int ptb_trace_closest(const ptb_scene *scene, const void *d_rays, int64_t n, int32_t precision,
+                      int32_t *d_tri, void *d_t, void *stream);
+
+/* replaces the sample loop x bounce loop of main() (main.py:186-271): for every pixel of the set and
+ * every sample in [s0, s1) it ADDS the sample's radiance to d_accum[pixel_slot] (float4: r, g, b,
+ * sample count).  The mean (main.py:274-280) is taken by ptb_tonemap / the caller. */
+size_t ptb_trace_paths_workspace(const ptb_render_params *p, int32_t samples_per_batch);
+int ptb_trace_paths(const ptb_scene *scene, const ptb_render_params *p, void *d_workspace,
+                    size_t workspace_bytes, float *d_accum /* [n_pixel_slots][4] */,
+                    const ptb_path_records *records /* may be NULL */, void *stream);
+
+/* replaces make_image (utils.py:150-161): d_accum is the FULL frame in ray-index order
+ * (slot = r); writes the H x W x 3 u8 image, rows top to bottom. d_workspace >= 64 bytes. */
+int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_rgb,
+                void *d_workspace, void *stream);
+
+/* scatter a shard's accumulation buffer (pixel-slot order) into a full-frame buffer (ray-index order) */
+int ptb_scatter_accum(const ptb_pixels *px, const float *d_accum_shard, float *d_accum_full, void *stream);
+
+int ptb_counters_read(const ptb_scene *scene, ptb_counters *out, void *stream); /* synchronises stream */
+int ptb_counters_reset(const ptb_scene *scene, void *stream);
+int64_t ptb_pixel_count(const ptb_pixels *px);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB_H */

@@ -1,0 +1,84 @@
+"""ctypes binding of libptb.so (include/ptb.h).  There is no CPU fallback: if the CUDA library is
+missing or a call fails, this module raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libptb.so")
+
+PREC_FP32, PREC_FP64 = 0, 1
+ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
+FLAG_NO_FP64_RETRACE, FLAG_SHARE_PRIMARY = 1, 2
+
+EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
+           "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
+           "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count"]
+
+
+class PtbError(RuntimeError):
+    pass
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("n_tri", C.c_int32), ("n_tri_obj", C.c_int32), ("n_obj", C.c_int32), ("n_light_tri", C.c_int32),
+                ("verts", C.c_void_p), ("normals", C.c_void_p), ("tri_obj", C.c_void_p), ("mat", C.c_void_p),
+                ("light_areas", C.c_void_p), ("eye", C.c_double * 3), ("ortho", C.c_double * 4),
+                ("ambient", C.c_double), ("light_color", C.c_double * 3), ("accel", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Pixels(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("shard", C.c_int32), ("n_shards", C.c_int32),
+                ("tile", C.c_int32), ("n_pixels", C.c_int32), ("d_pixels", C.c_void_p)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("px", Pixels), ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("bounces", C.c_int32),
+                ("seed", C.c_uint32), ("precision", C.c_int32), ("flags", C.c_int32),
+                ("samples_per_batch", C.c_int32), ("reserved", C.c_int32)]
+
+
+class PathRecords(C.Structure):
+    _fields_ = [("d_tri", C.c_void_p), ("d_contrib", C.c_void_p), ("d_k_after", C.c_void_p), ("d_lobe", C.c_void_p),
+                ("d_occ", C.c_void_p), ("d_leak", C.c_void_p), ("d_contrib64", C.c_void_p), ("d_k_after64", C.c_void_p)]
+
+
+class Counters(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("closest_rays", "shadow_rays", "shaded", "samples", "retraced", "launches",
+                                          "nodes_visited", "tris_tested")]
+
+
+_lib = None
+
+
+def lib():
+    """Load libptb.so (built in-tree by __graft_entry__.build()).  Raises if it is not there."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PtbError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'`; "
+                           "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.ptb_last_error.restype = C.c_char_p
+        L.ptb_trace_paths_workspace.restype = C.c_size_t
+        L.ptb_pixel_count.restype = C.c_int64
+        L.ptb_scene_create.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.POINTER(C.c_void_p)]
+        L.ptb_scene_destroy.argtypes = [C.c_void_p]
+        L.ptb_scene_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]
+        L.ptb_trace_primary.argtypes = [C.c_void_p, C.POINTER(Pixels), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ptb_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptb_trace_paths_workspace.argtypes = [C.POINTER(RenderParams), C.c_int32]
+        L.ptb_trace_paths.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
+                                      C.POINTER(PathRecords), C.c_void_p]
+        L.ptb_tonemap.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptb_scatter_accum.argtypes = [C.POINTER(Pixels), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptb_counters_read.argtypes = [C.c_void_p, C.POINTER(Counters), C.c_void_p]
+        L.ptb_counters_reset.argtypes = [C.c_void_p, C.c_void_p]
+        L.ptb_pixel_count.argtypes = [C.POINTER(Pixels)]
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        raise PtbError(f"{what} failed ({rc}): {lib().ptb_last_error().decode()}")

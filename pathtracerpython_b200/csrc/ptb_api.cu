@@ -1,0 +1,190 @@
+// ptb_api.cu - C ABI (include/ptb.h) over the wavefront kernels.  Host logic only: scene upload and
+// precompute, workspace carving, the per-batch / per-bounce launch sequence.
+#include <math.h>
+#include <stdarg.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "ptb_image.cuh"
+#include "ptb_shade64.cuh"
+
+namespace ptb {
+
+static thread_local char g_err[512] = "";
+unsigned long long g_launches = 0;
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+// persistent grid: a multiple of the SM count, capped by the work available
+static int grid_for(size_t work, int threads, int blocks_per_sm) {
+    size_t need = (work + threads - 1) / threads;
+    size_t cap = (size_t)num_sms() * blocks_per_sm;
+    return (int)std::max<size_t>(1, std::min(need, cap));
+}
+
+}  // namespace ptb
+
+using namespace ptb;
+
+struct ptb_scene {
+    DScene d;                       // device view handed to kernels by value
+    std::vector<void *> allocs;     // device allocations owned by the handle
+    int device;
+    float dt_scale;                 // FP32 error scale of the ray parameter (see ptb_isect.cuh)
+    double build_ms;
+    int n_nodes;
+};
+
+template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, const T **out, cudaStream_t st) {
+    void *p = nullptr;
+    size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
+    PTB_CUDA(cudaMalloc(&p, bytes));
+    s->allocs.push_back(p);
+    if (!h.empty()) PTB_CUDA(cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+    *out = (const T *)p;
+    return PTB_OK;
+}
+
+static inline float bits_f(int v) { float f; memcpy(&f, &v, 4); return f; }
+static inline void cross_h(const double *a, const double *b, double *c) {
+    c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
+}
+static inline double dot_h(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+// FP32 traversal record of one triangle (layout: ptb_scene.cuh)
+static TriRec make_trirec(const double *v, int obj, double scale) {
+    const double *A = v, *B = v + 3, *C = v + 6;
+    double ab[3], cb[3], n[3], e1[3], e2[3], N[3], mu[3], mv[3];
+    for (int i = 0; i < 3; ++i) { ab[i] = A[i] - B[i]; cb[i] = C[i] - B[i]; e1[i] = B[i] - A[i]; e2[i] = C[i] - A[i]; }
+    cross_h(ab, cb, n);                                  // utils.py:112-113
+    double nl = sqrt(dot_h(n, n));
+    for (int i = 0; i < 3; ++i) n[i] /= nl;
+    cross_h(e1, e2, N);
+    double inv = 1.0 / dot_h(N, N);
+    cross_h(e2, N, mu);
+    cross_h(N, e1, mv);
+    for (int i = 0; i < 3; ++i) { mu[i] *= inv; mv[i] *= inv; }
+    double mw[3] = {mu[0] + mv[0], mu[1] + mv[1], mu[2] + mv[2]};
+    double g = std::max(sqrt(dot_h(mu, mu)), std::max(sqrt(dot_h(mv, mv)), sqrt(dot_h(mw, mw))));
+    TriRec r;
+    r.q0 = make_float4((float)n[0], (float)n[1], (float)n[2], (float)dot_h(n, A));
+    r.q1 = make_float4((float)mu[0], (float)mu[1], (float)mu[2], (float)(-dot_h(A, mu)));
+    r.q2 = make_float4((float)mv[0], (float)mv[1], (float)mv[2], (float)(-dot_h(A, mv)));
+    r.q3 = make_float4((float)(32.0 * 5.9604644775390625e-08 * scale * g), 0.f, bits_f(obj), 0.f);
+    return r;
+}
+
+extern "C" const char *ptb_last_error(void) { return g_err; }
+extern "C" int ptb_version(void) { return 100; }
+
+extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out) {
+    if (!desc || !out) { set_error("ptb_scene_create: null argument"); return PTB_ERR_ARG; }
+    if (desc->n_tri <= 0 || desc->n_tri_obj < 0 || desc->n_tri_obj > desc->n_tri || desc->n_obj <= 0 ||
+        desc->n_light_tri != desc->n_tri - desc->n_tri_obj || desc->n_light_tri <= 0 || !desc->verts ||
+        !desc->normals || !desc->tri_obj || !desc->mat || !desc->light_areas) {
+        set_error("ptb_scene_create: inconsistent scene description");
+        return PTB_ERR_ARG;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int accel = desc->accel;
+    if (accel == PTB_ACCEL_AUTO) accel = desc->n_tri <= PTB_BRUTE_MAX_TRI ? PTB_ACCEL_BRUTE : PTB_ACCEL_LBVH;
+    if (accel == PTB_ACCEL_BRUTE && desc->n_tri > PTB_BRUTE_MAX_TRI) {
+        set_error("brute-force traversal holds at most %d triangles in shared memory", PTB_BRUTE_MAX_TRI);
+        return PTB_ERR_UNSUPPORTED;
+    }
+    if (accel != PTB_ACCEL_BRUTE) { set_error("LBVH traversal not built yet"); return PTB_ERR_UNSUPPORTED; }
+
+    ptb_scene *s = new ptb_scene();
+    memset(&s->d, 0, sizeof(DScene));
+    cudaGetDevice(&s->device);
+    const int n = desc->n_tri, no = desc->n_obj;
+    double scale = 1.0;
+    for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
+    for (int i = 0; i < 3; ++i) scale = std::max(scale, fabs(desc->eye[i]));
+    s->dt_scale = (float)(32.0 * 5.9604644775390625e-08 * scale);
+
+    std::vector<TriRec> tri(n);
+    std::vector<float4> sn(n);
+    std::vector<int> ids(n), tobj(desc->tri_obj, desc->tri_obj + n);
+    for (int i = 0; i < n; ++i) {
+        if (tobj[i] < 0 || tobj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
+        tri[i] = make_trirec(desc->verts + 9 * (size_t)i, tobj[i], scale);
+        const double *nn = desc->normals + 3 * (size_t)i;
+        sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(tobj[i]));
+        ids[i] = i;
+    }
+    std::vector<double> mat64((size_t)(no + 1) * 8, 0.0);
+    std::copy(desc->mat, desc->mat + (size_t)no * 8, mat64.begin());
+    std::vector<float> mat32(mat64.begin(), mat64.end());
+    std::vector<float4> lv((size_t)desc->n_light_tri * 3);
+    for (int i = 0; i < desc->n_light_tri * 3; ++i) {
+        const double *p = desc->verts + 9 * (size_t)desc->n_tri_obj + 3 * (size_t)i;
+        lv[i] = make_float4((float)p[0], (float)p[1], (float)p[2], 0.f);
+    }
+    std::vector<double> cdf(desc->n_light_tri + 1);
+    double acc = 0.0, total = 0.0;
+    cdf[0] = 0.0;
+    for (int i = 0; i < desc->n_light_tri; ++i) {       // utils.py:30-35: sequential FP64 sums
+        total = total + desc->light_areas[i];
+        acc = acc + desc->light_areas[i];
+        cdf[i + 1] = acc;
+    }
+    std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
+    std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
+
+    DScene &d = s->d;
+    int rc = PTB_OK;
+    if ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
+        (rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) || (rc = upload(s, verts, &d.verts64, st)) ||
+        (rc = upload(s, normals, &d.normals64, st)) || (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
+        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
+        ptb_scene_destroy(s);
+        return rc;
+    }
+    d.n_tri = n; d.n_tri_obj = desc->n_tri_obj; d.n_obj = no; d.n_light_tri = desc->n_light_tri;
+    d.accel = accel;
+    for (int i = 0; i < 3; ++i) { d.eye[i] = desc->eye[i]; d.light_color[i] = desc->light_color[i]; }
+    for (int i = 0; i < 4; ++i) d.ortho[i] = desc->ortho[i];
+    d.ambient = desc->ambient;
+    d.light_total = total;
+    s->build_ms = 0.0;
+    s->n_nodes = 0;
+    PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
+    *out = s;
+    return PTB_OK;
+}
+
+extern "C" int ptb_scene_destroy(ptb_scene *s) {
+    if (!s) return PTB_OK;
+    for (void *p : s->allocs) cudaFree(p);
+    delete s;
+    return PTB_OK;
+}
+
+extern "C" int ptb_scene_info(const ptb_scene *s, int32_t *accel, int32_t *n_nodes, double *build_ms) {
+    if (!s) { set_error("null scene"); return PTB_ERR_ARG; }
+    if (accel) *accel = s->d.accel;
+    if (n_nodes) *n_nodes = s->n_nodes;
+    if (build_ms) *build_ms = s->build_ms;
+    return PTB_OK;
+}
+
+extern "C" int64_t ptb_pixel_count(const ptb_pixels *px) { return px ? pixel_count(px) : 0; }
+
+#include "ptb_api_render.inl"

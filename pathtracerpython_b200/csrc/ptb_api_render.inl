@@ -1,0 +1,317 @@
+// ptb_api_render.inl - included by ptb_api.cu: the launch sequences behind ptb_trace_primary,
+// ptb_trace_closest, ptb_trace_paths, ptb_tonemap, ptb_scatter_accum and the counters.
+
+namespace ptb {
+
+// FP64 re-trace of uncertain FP32 primary rays (bounce 0: queue position == path id).
+__global__ void __launch_bounds__(128)
+k_retrace64(DScene sc, PixelMap pm, int npix, const unsigned *__restrict__ unc_count, const int *__restrict__ unc_list,
+            float *__restrict__ hit_t, int *__restrict__ hit_tri) {
+    const unsigned count = *unc_count;
+    for (unsigned u = blockIdx.x * blockDim.x + threadIdx.x; u < count; u += gridDim.x * blockDim.x) {
+        const int i = unc_list[u];
+        const int r = pm.ray_index(i % npix);
+        d3 o, d;
+        primary_ray64(sc, pm.W, pm.H, r, o, d);
+        const Hit64 h = closest_brute64(sc, o, d);
+        hit_tri[i] = h.tri;
+        if (h.tri >= 0) {
+            const d3 vr = xdiv3(d, xnorm(d));
+            hit_t[i] = (float)xdot(xsub3(h.P, o), vr);
+        } else {
+            hit_t[i] = 0.f;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sc.counters + CTR_RETRACED, (unsigned long long)count);
+}
+
+__global__ void k_rays_to_queue32(const float *__restrict__ rays, long long n, float4 *qo, float4 *qd, unsigned *count) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float *r = rays + 6 * i;
+        const float inv = rsqrtf(r[3] * r[3] + r[4] * r[4] + r[5] * r[5]);
+        qo[i] = make_float4(r[0], r[1], r[2], 1.f);
+        qd[i] = make_float4(r[3] * inv, r[4] * inv, r[5] * inv, __int_as_float((int)i));
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *count = (unsigned)n;
+}
+__global__ void k_rays_to_queue64(const double *__restrict__ rays, long long n, double4 *qo, double4 *qd, unsigned *count) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double *r = rays + 6 * i;
+        qo[i] = make_double4(r[0], r[1], r[2], 1.0);
+        qd[i] = make_double4(r[3], r[4], r[5], (double)i);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *count = (unsigned)n;
+}
+__global__ void k_cvt_d2f(const double *__restrict__ src, float *__restrict__ dst, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) dst[i] = (float)src[i];
+}
+
+static int check_scene(const ptb_scene *s) {
+    if (!s) { set_error("null scene handle"); return PTB_ERR_ARG; }
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (dev != s->device) { set_error("scene was created on device %d, current device is %d", s->device, dev); return PTB_ERR_ARG; }
+    return PTB_OK;
+}
+static int check_pixels(const ptb_pixels *px) {
+    if (!px || px->width <= 0 || px->height <= 0) { set_error("bad pixel set: width/height"); return PTB_ERR_ARG; }
+    if ((int64_t)px->width * px->height > 0x7fffffffll) { set_error("frame too large"); return PTB_ERR_ARG; }
+    if (!px->d_pixels && (px->n_shards > 1) && (px->shard < 0 || px->shard >= px->n_shards || px->tile <= 0)) {
+        set_error("bad pixel set: shard %d of %d, tile %d", px->shard, px->n_shards, px->tile);
+        return PTB_ERR_ARG;
+    }
+    return PTB_OK;
+}
+
+static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
+
+// closest-hit over queue `in` for the brute-force scene
+static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
+                            bool track, float *hit_t, int *hit_tri, cudaStream_t st) {
+    const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
+    if (track)
+        k_closest_brute32<true><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+    else
+        k_closest_brute32<false><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+}  // namespace ptb
+
+extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32_t precision, int32_t flags,
+                                 int32_t *d_tri, float *d_t, void *d_ws, size_t ws_bytes, void *stream) {
+    int rc;
+    if ((rc = check_scene(s)) || (rc = check_pixels(px))) return rc;
+    if (!d_tri || !d_t || !d_ws) { set_error("ptb_trace_primary: null output/workspace"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    BatchInfo bi;
+    bi.pm = make_pixel_map(px); bi.npix = bi.pm.n; bi.S = 1; bi.s_first = 0; bi.bounce = 0; bi.seed = 0;
+    const size_t n = (size_t)bi.npix;
+    if (n == 0) return PTB_OK;
+    if (precision == PTB_PREC_FP32) {
+        Queues<float> q;
+        if (!queue_carve<float>(d_ws, ws_bytes, n, 1, q)) { set_error("workspace too small: need %zu bytes", queue_bytes<float>(n, 1)); return PTB_ERR_NOMEM; }
+        k_gen<float><<<grid_for(n, 256, 8), 256, 0, st>>>(s->d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, 3);
+        PTB_LAUNCHED();
+        const bool track = !(flags & PTB_FLAG_NO_FP64_RETRACE);
+        if ((rc = launch_closest32(s, q, 0, q.count, n, track, d_t, d_tri, st))) return rc;
+        if (track) {
+            k_retrace64<<<grid_for(n / 8 + 1, 128, 4), 128, 0, st>>>(s->d, bi.pm, bi.npix, q.unc_count, q.unc_list, d_t, d_tri);
+            PTB_LAUNCHED();
+        }
+    } else if (precision == PTB_PREC_FP64) {
+        Queues<double> q;
+        if (!queue_carve<double>(d_ws, ws_bytes, n, 1, q)) { set_error("workspace too small: need %zu bytes", queue_bytes<double>(n, 1)); return PTB_ERR_NOMEM; }
+        k_gen<double><<<grid_for(n, 256, 8), 256, 0, st>>>(s->d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, 3);
+        PTB_LAUNCHED();
+        k_closest_brute64<<<grid_for(n, 128, 8), 128, 0, st>>>(s->d, q.qo[0], q.qd[0], q.count, q.hit_t, d_tri);
+        PTB_LAUNCHED();
+        k_cvt_d2f<<<grid_for(n, 256, 8), 256, 0, st>>>(q.hit_t, d_t, (long long)n);
+        PTB_LAUNCHED();
+    } else { set_error("unknown precision %d", precision); return PTB_ERR_ARG; }
+    return PTB_OK;
+}
+
+extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t n, int32_t precision,
+                                 int32_t *d_tri, void *d_t, void *stream) {
+    int rc;
+    if ((rc = check_scene(s))) return rc;
+    if (!d_rays || !d_tri || !d_t || n < 0) { set_error("ptb_trace_closest: bad argument"); return PTB_ERR_ARG; }
+    if (n == 0) return PTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    // small private scratch: two vec4 queues + count
+    const size_t v = precision == PTB_PREC_FP64 ? sizeof(double4) : sizeof(float4);
+    char *scratch = nullptr;
+    PTB_CUDA(cudaMallocAsync((void **)&scratch, 2 * v * (size_t)n + 256, st));
+    unsigned *cnt = (unsigned *)(scratch + 2 * v * (size_t)n);
+    if (precision == PTB_PREC_FP32) {
+        float4 *qo = (float4 *)scratch, *qd = qo + n;
+        k_rays_to_queue32<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float *)d_rays, n, qo, qd, cnt);
+        PTB_LAUNCHED();
+        Queues<float> q; memset(&q, 0, sizeof(q));
+        q.qo[0] = qo; q.qd[0] = qd;
+        if ((rc = launch_closest32(s, q, 0, cnt, (size_t)n, false, (float *)d_t, d_tri, st))) return rc;
+    } else {
+        double4 *qo = (double4 *)scratch, *qd = qo + n;
+        k_rays_to_queue64<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const double *)d_rays, n, qo, qd, cnt);
+        PTB_LAUNCHED();
+        k_closest_brute64<<<grid_for((size_t)n, 128, 8), 128, 0, st>>>(s->d, qo, qd, cnt, (double *)d_t, d_tri);
+        PTB_LAUNCHED();
+    }
+    PTB_CUDA(cudaFreeAsync(scratch, st));
+    return PTB_OK;
+}
+
+// ---------------------------------------------------------------- path tracing
+namespace ptb {
+
+template <typename T> static size_t per_path_bytes() { return queue_bytes<T>(1 << 20, 0) / (1 << 20) + 1; }
+
+static RecPtrs make_rec(const ptb_path_records *r, int npix, int n_samples, int bounces) {
+    RecPtrs p;
+    memset(&p, 0, sizeof(p));
+    p.npix = npix; p.n_samples = n_samples; p.bounces = bounces; p.s_off = 0;
+    if (r) {
+        p.tri = r->d_tri; p.contrib = r->d_contrib; p.k_after = r->d_k_after; p.lobe = r->d_lobe; p.occ = r->d_occ;
+        p.leak = r->d_leak; p.contrib64 = r->d_contrib64; p.k_after64 = r->d_k_after64;
+        p.any = p.tri || p.contrib || p.k_after || p.lobe || p.occ || p.leak || p.contrib64 || p.k_after64;
+    }
+    return p;
+}
+
+// one batch of S samples, FP32 product path
+static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<float> &q, BatchInfo bi, RecPtrs rec,
+                       float4 *accum, cudaStream_t st) {
+    int rc;
+    const size_t N = (size_t)bi.npix * bi.S;
+    const DScene &d = s->d;
+    k_gen<float><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
+    PTB_LAUNCHED();
+    for (int b = 0; b < p->bounces; ++b) {
+        const int in = b & 1, out = in ^ 1;
+        bi.bounce = b;
+        const bool track = (b == 0) && !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
+        if ((rc = launch_closest32(s, q, in, q.count + b, N, track, q.hit_t, q.hit_tri, st))) return rc;
+        if (track) {
+            k_retrace64<<<grid_for(N / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
+            PTB_LAUNCHED();
+        }
+        k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
+            d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
+            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec);
+        PTB_LAUNCHED();
+        k_shadow_brute32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem_tris(d.n_tri_obj), st>>>(
+            d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        PTB_LAUNCHED();
+    }
+    k_reduce<float><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+// one batch, FP64 validation path (reference operation order)
+static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<double> &q, BatchInfo bi, RecPtrs rec,
+                       float4 *accum, cudaStream_t st) {
+    const size_t N = (size_t)bi.npix * bi.S;
+    const DScene &d = s->d;
+    k_gen<double><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
+    PTB_LAUNCHED();
+    for (int b = 0; b < p->bounces; ++b) {
+        const int in = b & 1, out = in ^ 1;
+        bi.bounce = b;
+        k_closest_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri);
+        PTB_LAUNCHED();
+        k_shade64<<<grid_for(N, PTB_SHADE_THREADS, 4), PTB_SHADE_THREADS, 0, st>>>(
+            d, bi, q.qo[in], q.qd[in], q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out], q.sh_p, q.sh_d,
+            q.sh_aux, q.L, q.cap, rec);
+        PTB_LAUNCHED();
+        k_shadow_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        PTB_LAUNCHED();
+    }
+    k_reduce<double><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+}  // namespace ptb
+
+extern "C" size_t ptb_trace_paths_workspace(const ptb_render_params *p, int32_t samples_per_batch) {
+    if (!p) return 0;
+    const size_t npix = (size_t)pixel_count(&p->px);
+    const size_t cap = npix * (size_t)std::max(1, samples_per_batch);
+    return p->precision == PTB_PREC_FP64 ? queue_bytes<double>(cap, p->bounces) : queue_bytes<float>(cap, p->bounces);
+}
+
+extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
+                               float *d_accum, const ptb_path_records *records, void *stream) {
+    int rc;
+    if ((rc = check_scene(s))) return rc;
+    if (!p || (rc = check_pixels(&p->px))) return rc ? rc : PTB_ERR_ARG;
+    if (!d_ws || !d_accum) { set_error("ptb_trace_paths: null workspace/accum"); return PTB_ERR_ARG; }
+    if (p->sample_end < p->sample_begin || p->bounces < 0) { set_error("bad sample range / bounces"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int npix = (int)pixel_count(&p->px);
+    const int n_samples = p->sample_end - p->sample_begin;
+    if (npix == 0 || n_samples == 0) return PTB_OK;
+    const bool f64 = p->precision == PTB_PREC_FP64;
+    if (!f64 && p->precision != PTB_PREC_FP32) { set_error("unknown precision %d", p->precision); return PTB_ERR_ARG; }
+    // samples per batch: as many as the workspace holds (or the caller's cap)
+    int S = p->samples_per_batch > 0 ? p->samples_per_batch : n_samples;
+    S = std::min(S, n_samples);
+    while (S >= 1) {
+        size_t need = f64 ? queue_bytes<double>((size_t)npix * S, p->bounces) : queue_bytes<float>((size_t)npix * S, p->bounces);
+        if (need <= ws_bytes && (size_t)npix * S < 0x7fffffffull) break;
+        S = (p->samples_per_batch > 0) ? 0 : S / 2;
+    }
+    if (S < 1) {
+        set_error("workspace too small: %zu bytes cannot hold one sample of %d pixels (need %zu)", ws_bytes, npix,
+                  f64 ? queue_bytes<double>((size_t)npix, p->bounces) : queue_bytes<float>((size_t)npix, p->bounces));
+        return PTB_ERR_NOMEM;
+    }
+    RecPtrs rec = make_rec(records, npix, n_samples, p->bounces);
+    if (rec.any) {
+        const size_t n = (size_t)npix * n_samples * p->bounces;
+        k_init_records<<<grid_for(n, 256, 8), 256, 0, st>>>(rec, n);
+        PTB_LAUNCHED();
+    }
+    BatchInfo bi;
+    bi.pm = make_pixel_map(&p->px); bi.npix = npix; bi.seed = p->seed; bi.bounce = 0;
+    Queues<float> q32; Queues<double> q64;
+    if (f64) queue_carve<double>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q64);
+    else queue_carve<float>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q32);
+    for (int s0 = p->sample_begin; s0 < p->sample_end; s0 += S) {
+        bi.S = std::min(S, p->sample_end - s0);
+        bi.s_first = s0;
+        rec.s_off = s0 - p->sample_begin;
+        rc = f64 ? run_batch64(s, p, q64, bi, rec, (float4 *)d_accum, st) : run_batch32(s, p, q32, bi, rec, (float4 *)d_accum, st);
+        if (rc) return rc;
+    }
+    return PTB_OK;
+}
+
+extern "C" int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_rgb, void *d_ws, void *stream) {
+    if (!d_accum || !d_rgb || !d_ws || width <= 0 || height <= 0) { set_error("ptb_tonemap: bad argument"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long *mm = (unsigned long long *)d_ws;
+    const int n = width * height;
+    k_minmax_init<<<1, 1, 0, st>>>(mm);
+    PTB_LAUNCHED();
+    k_minmax<<<grid_for((size_t)n, 256, 4), 256, 0, st>>>((const float4 *)d_accum, n, mm);
+    PTB_LAUNCHED();
+    k_quantise<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float4 *)d_accum, width, height, mm, d_rgb);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+extern "C" int ptb_scatter_accum(const ptb_pixels *px, const float *d_src, float *d_dst, void *stream) {
+    int rc;
+    if ((rc = check_pixels(px))) return rc;
+    if (!d_src || !d_dst) { set_error("ptb_scatter_accum: null pointer"); return PTB_ERR_ARG; }
+    PixelMap pm = make_pixel_map(px);
+    if (pm.n == 0) return PTB_OK;
+    k_scatter_accum<<<grid_for((size_t)pm.n, 256, 8), 256, 0, (cudaStream_t)stream>>>(pm, (const float4 *)d_src, (float4 *)d_dst);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+extern "C" int ptb_counters_read(const ptb_scene *s, ptb_counters *out, void *stream) {
+    int rc;
+    if ((rc = check_scene(s))) return rc;
+    if (!out) { set_error("null counters"); return PTB_ERR_ARG; }
+    unsigned long long h[CTR_COUNT];
+    PTB_CUDA(cudaMemcpyAsync(h, s->d.counters, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PTB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    out->closest_rays = h[CTR_CLOSEST]; out->shadow_rays = h[CTR_SHADOW]; out->shaded = h[CTR_SHADED];
+    out->samples = h[CTR_SAMPLES]; out->retraced = h[CTR_RETRACED]; out->launches = g_launches;
+    out->nodes_visited = h[CTR_NODES]; out->tris_tested = h[CTR_TRIS];
+    return PTB_OK;
+}
+
+extern "C" int ptb_counters_reset(const ptb_scene *s, void *stream) {
+    int rc;
+    if ((rc = check_scene(s))) return rc;
+    PTB_CUDA(cudaMemsetAsync(s->d.counters, 0, CTR_COUNT * sizeof(unsigned long long), (cudaStream_t)stream));
+    g_launches = 0;
+    return PTB_OK;
+}

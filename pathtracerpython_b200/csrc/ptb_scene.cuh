@@ -1,0 +1,53 @@
+// ptb_scene.cuh - device-resident scene (immutable after ptb_scene_create) and its HBM layout.
+#pragma once
+#include "ptb_common.cuh"
+
+namespace ptb {
+
+// FP32 traversal record, 64 B per triangle (4 x float4, one 128 B line holds two triangles):
+//   q0 = (n.x, n.y, n.z, d0)     unit plane normal as utils.py:112-114 builds it, d0 = n . v1
+//   q1 = (mu.x, mu.y, mu.z, cu)  u(P) = mu . P + cu   barycentric weight of v2
+//   q2 = (mv.x, mv.y, mv.z, cv)  v(P) = mv . P + cv   barycentric weight of v3
+//   q3 = (eps, -, obj_id bits, -) eps = conservative FP32 error scale of u, v (see isect)
+// in_triangle (utils.py:72-91) accepts exactly the points with u > 0, v > 0, u + v < 1.
+struct TriRec { float4 q0, q1, q2, q3; };
+
+// BVH2 node, 64 B: both children's boxes inline so one fetch decides both descents.
+//   lo0.xyz hi0.xyz = child 0 box, lo1.xyz hi1.xyz = child 1 box,
+//   c0 / c1 = child index (>= 0 inner node, < 0 : leaf, triangle slot = ~c)
+struct BvhNode {
+    float lo0x, lo0y, lo0z, hi0x, hi0y, hi0z;
+    float lo1x, lo1y, lo1z, hi1x, hi1y, hi1z;
+    int c0, c1, n0, n1;   // n0/n1: triangle count under the child (leaf: 1)
+};
+
+struct DScene {
+    // --- FP32 product path
+    const TriRec *tri;        // [n_tri] in reference order (brute force) or BVH leaf order
+    const int *tri_id;        // [n_tri] slot -> reference triangle index (identity for brute force)
+    const float4 *tri_sn;     // [n_tri] by reference index: stored normal xyz (scene_reader.py:5-8), w = obj id bits
+    const float *mat32;       // [n_obj+1][8] r g b ka kd ks kt n (row n_obj = light, zeros)
+    const float4 *light_v32;  // [n_light_tri][3]
+    // --- FP64 exact path (reference formulas on the parsed vertices)
+    const double *verts64;    // [n_tri][9]
+    const double *normals64;  // [n_tri][3]
+    const double *mat64;      // [n_obj+1][8]
+    const double *light_cdf;  // [n_light_tri+1] running sums of light_obj.areas (utils.py:31-35)
+    const int *tri_obj;       // [n_tri]
+    // --- acceleration structure (accel == PTB_ACCEL_LBVH)
+    const BvhNode *nodes;     // [n_tri-1]; root = 0
+    const BvhNode *nodes_occ; // BVH over the occlusion set (object triangles only)
+    const TriRec *tri_occ;    // leaf-ordered records of the occlusion set
+    const int *tri_id_occ;
+    int n_tri, n_tri_obj, n_obj, n_light_tri;
+    int accel;
+    double eye[3], ortho[4], ambient, light_color[3];
+    double light_total;       // sum(areas) (utils.py:30)
+    unsigned long long *counters;   // device ptb_counters (first 8 u64) + queue counters
+};
+
+// offsets into DScene::counters (u64 units)
+enum { CTR_CLOSEST = 0, CTR_SHADOW = 1, CTR_SHADED = 2, CTR_SAMPLES = 3, CTR_RETRACED = 4, CTR_LAUNCHES = 5,
+       CTR_NODES = 6, CTR_TRIS = 7, CTR_COUNT = 8 };
+
+}  // namespace ptb

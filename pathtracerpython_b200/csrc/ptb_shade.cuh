@@ -1,0 +1,183 @@
+// ptb_shade.cuh - camera-ray generation, shading / bounce kernels with fused stream compaction.
+//
+// k_gen      : make_screen_pts + make_rays (utils.py:55-69, main.py:191) for a batch of paths.
+// k_shade32  : per live path: miss / light hit / shaded (main.py:212-221); for shaded paths it
+//              draws the 3 light samples (utils.py:21-46) and writes the shadow work item, then takes
+//              the bounce step (main.py:236-268) and writes the next ray.  Survivors are compacted
+//              with a warp ballot + block prefix sum + one atomic per block, so the next bounce's
+//              queues are dense (north_star (2)).
+// k_shade64  : the same in the reference's FP64 operation order (mirrors oracle/pt_oracle.c).
+#pragma once
+#include "ptb_shadow.cuh"
+
+namespace ptb {
+
+#define PTB_SHADE_THREADS 256
+
+struct BatchInfo {
+    PixelMap pm;
+    int npix;        // pixels in the call's set
+    int S;           // samples in this batch
+    int s_first;     // absolute index of the batch's first sample
+    int bounce;
+    uint32_t seed;
+};
+
+// ---------------------------------------------------------------- camera rays
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_gen(DScene sc, BatchInfo bi, typename VecT<T>::v4 *__restrict__ qo, typename VecT<T>::v4 *__restrict__ qd,
+      typename VecT<T>::v4 *__restrict__ L, unsigned *count, unsigned *unc_count, int n_counts) {
+    const unsigned N = (unsigned)bi.npix * (unsigned)bi.S;
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < N; j += gridDim.x * blockDim.x) {
+        const int p = (int)(j % (unsigned)bi.npix);
+        const int r = bi.pm.ray_index(p);
+        d3 o, d;
+        primary_ray64(sc, bi.pm.W, bi.pm.H, r, o, d);
+        if (sizeof(T) == 4) d = xdiv3(d, xnorm(d));     // FP32 queues carry unit directions
+        qo[j] = mk4((T)o.x, (T)o.y, (T)o.z, (T)1);
+        qd[j] = mk4((T)d.x, (T)d.y, (T)d.z, id_pack((T)0, (int)j));
+        L[j] = mk4((T)0, (T)0, (T)0, (T)0);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        count[0] = N;
+        for (int i = 1; i < n_counts; ++i) count[i] = 0;
+        unc_count[0] = 0;
+        atomicAdd(sc.counters + CTR_SAMPLES, (unsigned long long)N);
+    }
+}
+
+// block-wide exclusive scan of a predicate; returns this thread's output slot (valid when alive) and
+// reserves `total` slots in *d_out_count with one atomic.
+__device__ __forceinline__ unsigned compact_slot(bool alive, unsigned *d_out_count) {
+    __shared__ unsigned s_warp[PTB_SHADE_THREADS / 32];
+    __shared__ unsigned s_base;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned ballot = __ballot_sync(0xffffffffu, alive);
+    if (lane == 0) s_warp[warp] = __popc(ballot);
+    __syncthreads();
+    unsigned before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < PTB_SHADE_THREADS / 32; ++w) {
+        const unsigned c = s_warp[w];
+        if (w < (int)warp) before += c;
+        total += c;
+    }
+    if (threadIdx.x == 0) s_base = total ? atomicAdd(d_out_count, total) : 0u;
+    __syncthreads();
+    const unsigned slot = s_base + before + __popc(ballot & ((1u << lane) - 1u));
+    __syncthreads();   // s_warp / s_base are reused by the next tile
+    return slot;
+}
+
+// light triangle pick: first i with cum[i] <= x < cum[i+1] (utils.py:28-39), FP64 so the discrete
+// choice is identical to the reference's.
+__device__ __forceinline__ int pick_light(const double *cdf, int n, double x) {
+    int lo = 0, hi = n;               // invariant: cdf[lo] <= x (cdf[0] = 0), answer in [lo, hi)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(cdf + mid) <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(PTB_SHADE_THREADS)
+k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
+          const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
+          unsigned *d_count_out, float4 *__restrict__ qo_out, float4 *__restrict__ qd_out,
+          float4 *__restrict__ sh_p, float4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, float4 *__restrict__ L,
+          int cap, RecPtrs rec) {
+    const unsigned count = *d_count_in;
+    const float ex = (float)sc.eye[0], ey = (float)sc.eye[1], ez = (float)sc.eye[2];
+    for (unsigned base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
+        const unsigned i = base + threadIdx.x;
+        bool alive = false;
+        float4 a, b; float t = 0.f; int tri = -1, id = 0, obj = 0;
+        float4 sn = make_float4(0, 0, 0, 0);
+        if (i < count) {
+            a = qo[i]; b = qd[i]; t = hit_t[i]; tri = hit_tri[i];
+            id = id_unpack(b.w);
+            if (tri >= 0) {
+                sn = __ldg(sc.tri_sn + tri);
+                obj = __float_as_int(sn.w);
+                if (obj == sc.n_obj) {                      // light hit: main.py:214-215, 265-266
+                    float4 l = L[id];
+                    const float c0 = (float)sc.light_color[0] * a.w, c1 = (float)sc.light_color[1] * a.w, c2 = (float)sc.light_color[2] * a.w;
+                    l.x += c0; l.y += c1; l.z += c2;
+                    L[id] = l;
+                    if (rec.any) {
+                        const size_t ri = rec.index(id, bi.bounce);
+                        if (rec.contrib) { rec.contrib[3 * ri] = c0; rec.contrib[3 * ri + 1] = c1; rec.contrib[3 * ri + 2] = c2; }
+                        if (rec.k_after) rec.k_after[ri] = a.w;
+                    }
+                } else {
+                    alive = true;
+                }
+            }
+            if (rec.any && rec.tri) rec.tri[rec.index(id, bi.bounce)] = tri;
+        }
+        const unsigned j = compact_slot(alive, d_count_out);
+        if (!alive) continue;
+
+        const f3 o = mk3(a.x, a.y, a.z), d = mk3(b.x, b.y, b.z), n = mk3(sn.x, sn.y, sn.z);
+        const float k = a.w;
+        const f3 P = mk3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
+        const int s_local = id / bi.npix, p = id - s_local * bi.npix;
+        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
+
+        // ---- 3 light samples (main.py:30-40)
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+            const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);
+            const int li = pick_light(sc.light_cdf, sc.n_light_tri, sc.light_total * u01<double>(w.x));
+            const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
+            const float inv = 1.0f / ((c0 + c1) + c2);
+            const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
+            const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
+            const f3 v = mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)) - P.x,
+                             fmaf(wc, v3.y, fmaf(wb, v2.y, wa * v1.y)) - P.y,
+                             fmaf(wc, v3.z, fmaf(wb, v2.z, wa * v1.z)) - P.z);
+            const float d2 = dot(v, v);
+            const float rn = rsqrtf(d2);
+            sh_d[(size_t)s * cap + j] = make_float4(v.x * rn, v.y * rn, v.z * rn, d2);
+        }
+        sh_p[j] = make_float4(P.x, P.y, P.z, k);
+        sh_aux[j] = make_int2(id, tri);
+
+        // ---- bounce (main.py:240-264)
+        const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, 3u);
+        const double kd = __ldg(sc.mat64 + 8 * obj + 4), ks = __ldg(sc.mat64 + 8 * obj + 5);
+        const bool diffuse = ((kd + ks) * u01<double>(w.x)) <= kd;
+        const float cy = n.y, sy = sqrtf(fmaxf(0.f, fmaf(-cy, cy, 1.0f)));   // cos / sin of arccos(n.y)
+        f3 v; float knew;
+        if (diffuse) {
+            const float u1 = u01<float>(w.y), u2 = u01<float>(w.z);
+            const float sp = sqrtf(1.0f - u1), cp = sqrtf(u1);               // sin / cos of arccos(sqrt(u1))
+            float st, ct;
+            sincosf(6.28f * u2, &st, &ct);                                   // TAU = 6.28 (main.py:19)
+            v = mk3(sp * ct, sp * st, cp);
+        } else {
+            const float dn2 = 2.0f * dot(n, d);
+            v = mk3(fmaf(dn2, n.x, -d.x), fmaf(dn2, n.y, -d.y), fmaf(dn2, n.z, -d.z));
+            const float rn = rsqrtf(dot(v, v));
+            v = v * rn;
+        }
+        const f3 wv = mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));   // R_y(arccos(n.y)) (main.py:148-162)
+        if (diffuse) {
+            knew = k * ((float)kd * dot(wv, n));
+        } else {
+            f3 e = mk3(ex - P.x, ey - P.y, ez - P.z);
+            e = e * rsqrtf(dot(e, e));
+            knew = k * ((float)ks * powf(dot(e, wv), __ldg(sc.mat32 + 8 * obj + 7)));
+        }
+        qo_out[j] = make_float4(P.x, P.y, P.z, knew);
+        qd_out[j] = make_float4(wv.x, wv.y, wv.z, __int_as_float(id));
+        if (rec.any) {
+            const size_t ri = rec.index(id, bi.bounce);
+            if (rec.lobe) rec.lobe[ri] = diffuse ? 0 : 1;
+            if (rec.k_after) rec.k_after[ri] = knew;
+        }
+    }
+}
+
+}  // namespace ptb

@@ -1,0 +1,215 @@
+"""Host side of the hot path: the replacement for main.py's sample/bounce loops (main.py:165-293).
+
+`render(scene_or_path, n_rays, n_bounces)` -> PIL.Image is the drop-in for `main()`'s body: same
+inputs (`Scene`, `-r`, `-b`), same output (`make_image`'s 8-bit RGB image).  `Renderer` is the
+lower-level object: it owns the device scene handle (libptb.so) and the torch tensors used as
+workspace / accumulation buffers, and exposes the three parity seams:
+
+    trace_primary()  <-> one round of intersect_objects over the primary rays  (main.py:199-204)
+    trace_paths()    <-> the sample loop x bounce loop                         (main.py:186-271)
+    image()          <-> make_image                                           (utils.py:150-161)
+
+PyTorch is used for device memory and streams only; all arithmetic happens in libptb.so.  There is
+no CPU fallback: without CUDA or without the library these calls raise.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import PtbError
+from .scene import Scene
+
+
+def _torch():
+    import torch
+    if not torch.cuda.is_available():
+        raise PtbError("CUDA device required: pathtracerpython_b200 has no CPU fallback")
+    return torch
+
+
+class Renderer:
+    def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None):
+        torch = _torch()
+        self.torch = torch
+        self.scene = Scene(scene) if isinstance(scene, str) else scene
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        self.flat = self.scene.flatten() if hasattr(self.scene, "flatten") else self.scene
+        self.width, self.height = int(self.flat["width"]), int(self.flat["height"])
+        self.workspace_bytes = workspace_bytes
+        self._ws = None
+        self._handle = C.c_void_p()
+        f = self.flat
+        self._keep = [np.ascontiguousarray(f[k], dt) for k, dt in
+                      (("verts", np.float64), ("normals", np.float64), ("tri_obj", np.int32), ("mat", np.float64),
+                       ("light_areas", np.float64))]
+        d = _lib.SceneDesc()
+        d.n_tri = self._keep[0].shape[0]
+        d.n_tri_obj = int(f["n_tri_obj"])
+        d.n_obj = self._keep[3].shape[0]
+        d.n_light_tri = d.n_tri - d.n_tri_obj
+        d.verts, d.normals, d.tri_obj, d.mat, d.light_areas = [a.ctypes.data for a in self._keep]
+        d.eye[:] = [float(x) for x in f["eye"]]
+        d.ortho[:] = [float(x) for x in f["ortho"]]
+        d.ambient = float(f["ambient"])
+        d.light_color[:] = [float(x) for x in f["light_color"][:3]]
+        d.accel = accel
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_scene_create(C.byref(d), self._stream(), C.byref(self._handle)), "ptb_scene_create")
+        self.n_tri = d.n_tri
+
+    # ---- plumbing
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "_handle", None) and self._handle.value:
+            _lib.lib().ptb_scene_destroy(self._handle)
+            self._handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def pixels(self, width=None, height=None, shard=0, n_shards=1, tile=4096, pixel_list=None):
+        px = _lib.Pixels()
+        px.width = int(width or self.width)
+        px.height = int(height or self.height)
+        px.shard, px.n_shards, px.tile = int(shard), int(n_shards), int(tile)
+        keep = None
+        if pixel_list is not None:
+            keep = self.torch.as_tensor(np.asarray(pixel_list, np.int32), device=self.device)
+            px.n_pixels = keep.numel()
+            px.d_pixels = keep.data_ptr()
+        return px, keep
+
+    def pixel_count(self, px):
+        return int(_lib.lib().ptb_pixel_count(C.byref(px)))
+
+    def workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = self.torch.empty(int(nbytes), dtype=self.torch.uint8, device=self.device)
+        return self._ws
+
+    # ---- parity seam 1
+    def trace_primary(self, width=None, height=None, pixel_list=None, precision=_lib.PREC_FP32, flags=0):
+        """Closest-hit triangle id (-1 = miss) and ray parameter for the primary rays."""
+        torch = self.torch
+        px, keep = self.pixels(width, height, pixel_list=pixel_list)
+        n = self.pixel_count(px)
+        tri = torch.empty(n, dtype=torch.int32, device=self.device)
+        t = torch.empty(n, dtype=torch.float32, device=self.device)
+        ws = self.workspace(max(1 << 20, n * 400))
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_trace_primary(self._handle, C.byref(px), precision, flags, tri.data_ptr(), t.data_ptr(),
+                                                    ws.data_ptr(), ws.numel(), self._stream()), "ptb_trace_primary")
+        return tri, t
+
+    def trace_closest(self, rays, precision=_lib.PREC_FP32):
+        """intersect_objects for caller-supplied rays [n, 6] (origin, direction)."""
+        torch = self.torch
+        dt = torch.float64 if precision == _lib.PREC_FP64 else torch.float32
+        rays = torch.as_tensor(np.asarray(rays), device=self.device).to(dt).contiguous().reshape(-1, 6)
+        n = rays.shape[0]
+        tri = torch.empty(n, dtype=torch.int32, device=self.device)
+        t = torch.empty(n, dtype=dt, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_trace_closest(self._handle, rays.data_ptr(), n, precision, tri.data_ptr(), t.data_ptr(),
+                                                    self._stream()), "ptb_trace_closest")
+        return tri, t
+
+    # ---- parity seam 2 / the hot path
+    def trace_paths(self, n_rays, n_bounces, seed=0, width=None, height=None, shard=0, n_shards=1, tile=4096,
+                    pixel_list=None, sample_begin=0, precision=_lib.PREC_FP32, flags=0, records=False, accum=None,
+                    samples_per_batch=0):
+        """Adds samples [sample_begin, sample_begin + n_rays) of every pixel of the set to `accum`
+        ([n_pixel_slots, 4] float32: r, g, b sums and sample count).  Returns (accum, records | None)."""
+        torch = self.torch
+        p = _lib.RenderParams()
+        p.px, keep = self.pixels(width, height, shard, n_shards, tile, pixel_list)
+        npix = self.pixel_count(p.px)
+        p.sample_begin, p.sample_end = int(sample_begin), int(sample_begin + n_rays)
+        p.bounces, p.seed, p.precision, p.flags = int(n_bounces), int(seed) & 0xFFFFFFFF, precision, flags
+        p.samples_per_batch = int(samples_per_batch)
+        if accum is None:
+            accum = torch.zeros((npix, 4), dtype=torch.float32, device=self.device)
+        rec, rec_t = None, None
+        if records:
+            sh = (npix, n_rays, n_bounces)
+            rec_t = {"tri": torch.empty(sh, dtype=torch.int32, device=self.device),
+                     "contrib": torch.empty(sh + (3,), dtype=torch.float32, device=self.device),
+                     "k_after": torch.empty(sh, dtype=torch.float32, device=self.device),
+                     "lobe": torch.empty(sh, dtype=torch.int8, device=self.device),
+                     "occ": torch.empty(sh, dtype=torch.int8, device=self.device),
+                     "leak": torch.empty(sh, dtype=torch.int8, device=self.device)}
+            if precision == _lib.PREC_FP64:
+                rec_t["contrib64"] = torch.empty(sh + (3,), dtype=torch.float64, device=self.device)
+                rec_t["k_after64"] = torch.empty(sh, dtype=torch.float64, device=self.device)
+            rec = _lib.PathRecords()
+            for k, v in rec_t.items():
+                setattr(rec, "d_" + k, v.data_ptr())
+        L = _lib.lib()
+        if self.workspace_bytes:
+            ws_bytes = self.workspace_bytes
+        else:
+            # default: as many samples per batch as fit in ~1/4 of free memory, at most all of them
+            free, _ = torch.cuda.mem_get_info(self.device)
+            one = L.ptb_trace_paths_workspace(C.byref(p), 1)
+            spb = max(1, min(n_rays, int((free // 4) // max(one, 1)), (2 ** 31 - 1) // max(npix, 1)))
+            if samples_per_batch:
+                spb = min(spb, samples_per_batch)
+            ws_bytes = L.ptb_trace_paths_workspace(C.byref(p), spb)
+        ws = self.workspace(ws_bytes)
+        with torch.cuda.device(self.device):
+            _lib.check(L.ptb_trace_paths(self._handle, C.byref(p), ws.data_ptr(), ws.numel(), accum.data_ptr(),
+                                         C.byref(rec) if rec is not None else None, self._stream()), "ptb_trace_paths")
+        return accum, rec_t
+
+    # ---- output seam
+    def image(self, accum_full, width=None, height=None):
+        """make_image on a full-frame accumulation buffer (ray-index order) -> uint8 tensor [H, W, 3]."""
+        torch = self.torch
+        W, H = int(width or self.width), int(height or self.height)
+        rgb = torch.empty((H, W, 3), dtype=torch.uint8, device=self.device)
+        ws = self.workspace(256)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_tonemap(accum_full.data_ptr(), W, H, rgb.data_ptr(), ws.data_ptr(), self._stream()),
+                       "ptb_tonemap")
+        return rgb
+
+    def scatter(self, px, accum_shard, accum_full):
+        with self.torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_scatter_accum(C.byref(px), accum_shard.data_ptr(), accum_full.data_ptr(), self._stream()),
+                       "ptb_scatter_accum")
+        return accum_full
+
+    def counters(self, reset=False):
+        c = _lib.Counters()
+        with self.torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_counters_read(self._handle, C.byref(c), self._stream()), "ptb_counters_read")
+            if reset:
+                _lib.check(_lib.lib().ptb_counters_reset(self._handle, self._stream()), "ptb_counters_reset")
+        return {k: int(getattr(c, k)) for k, _ in _lib.Counters._fields_}
+
+
+def render(scene, n_rays=1, n_bounces=1, seed=None, width=None, height=None, device=None, precision=_lib.PREC_FP32,
+           flags=0, return_radiance=False):
+    """Drop-in for the body of main() (main.py:165-293): scene (path or Scene) -> PIL.Image.
+    `seed` defaults to the scene's `seed` keyword (parsed but unused by the reference, A-Q19)."""
+    from PIL import Image
+    r = Renderer(scene, device=device)
+    try:
+        if seed is None:
+            seed = r.flat.get("seed") or 0
+        accum, _ = r.trace_paths(n_rays, n_bounces, seed=seed, width=width, height=height, precision=precision, flags=flags)
+        rgb = r.image(accum, width, height)
+        im = Image.fromarray(rgb.cpu().numpy())
+        if return_radiance:
+            a = accum.cpu().numpy()
+            return im, a[:, :3] / np.maximum(a[:, 3:4], 1)
+        return im
+    finally:
+        r.close()

@@ -1,0 +1,212 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every call goes through the C ABI
+(libptb.so via ctypes); the oracle is the checker only.
+
+Three north-star checks:
+  1. primary-ray closest-hit triangle ids and hit/miss masks: bit-exact;
+  2. per-path radiance under the identical injected Philox stream: FP64 mode to 1e-9 with every discrete
+     outcome identical; FP32 mode |d| <= 1e-4 + 1e-3 |ref| on paths whose discrete history matches,
+     divergent paths counted (target < 100 ppm of path-bounces... stated per test);
+  3. images: u8 image from the GPU radiance == oracle make_image of the same radiance; against the
+     reference's own image +-1 LSB on >= 99 % of values.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import pathtracerpython_b200 as ptb
+from oracle import oracle, scene_port
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+ATOL, RTOL = 1e-4, 1e-3       # FP32 per-path radiance tolerance
+
+
+def g(name):
+    return np.load(os.path.join(GOLDEN, name))
+
+
+@pytest.fixture(scope="module")
+def flat():
+    return scene_port.load_scene(ptb.CORNELL_SDL)
+
+
+@pytest.fixture(scope="module")
+def rnd():
+    r = ptb.Renderer(ptb.CORNELL_SDL, device=0)
+    yield r
+    r.close()
+
+
+# ------------------------------------------------------------------ check 1
+@pytest.mark.parametrize("prec", [ptb.PREC_FP32, ptb.PREC_FP64])
+def test_primary_ids_golden(rnd, prec):
+    gold = g("cornell_primary.npz")
+    tri, _ = rnd.trace_primary(precision=prec)
+    assert np.array_equal(tri.cpu().numpy(), gold["tri_40"])
+    for res in (512, 1024):
+        tri, _ = rnd.trace_primary(res, res, pixel_list=gold[f"pixels_{res}"], precision=prec)
+        assert np.array_equal(tri.cpu().numpy(), gold[f"tri_{res}"])
+
+
+@pytest.mark.parametrize("res", [40, 41, 512, 1024])
+def test_primary_ids_full_frame_vs_oracle(rnd, flat, res):
+    want, d2, _ = oracle.Oracle(flat, res, res).primary()
+    tri, t = rnd.trace_primary(res, res)
+    tri, t = tri.cpu().numpy(), t.cpu().numpy()
+    assert np.array_equal(tri, want)                      # bit-exact ids and hit/miss mask
+    hit = want >= 0
+    assert np.allclose(np.abs(t[hit]), np.sqrt(d2[hit]), rtol=1e-5)
+    # the FP64 re-trace must only touch a small fraction of rays
+    c = rnd.counters(reset=True)
+    assert c["retraced"] <= 0.02 * res * res + 16
+
+
+def test_primary_fp32_without_retrace_is_close(rnd, flat):
+    want, _, _ = oracle.Oracle(flat, 512, 512).primary()
+    tri, _ = rnd.trace_primary(512, 512, flags=ptb.FLAG_NO_FP64_RETRACE)
+    assert (tri.cpu().numpy() != want).mean() < 1e-4
+
+
+def test_closest_line_semantics_random_rays(rnd, flat):
+    rng = np.random.default_rng(5)
+    n = 20000
+    o = np.stack([rng.uniform(-3.5, 3.5, n), rng.uniform(-3.5, 3.5, n), rng.uniform(-32, -17, n)], 1)
+    d = rng.normal(size=(n, 3))
+    rays = np.concatenate([o, d], 1)
+    want, d2, _ = oracle.Oracle(flat).closest(rays)
+    tri64, t64 = rnd.trace_closest(rays, ptb.PREC_FP64)
+    assert np.array_equal(tri64.cpu().numpy(), want)
+    assert np.allclose(t64.cpu().numpy() ** 2, d2, rtol=1e-12, atol=1e-12)
+    tri32, _ = rnd.trace_closest(rays.astype(np.float32), ptb.PREC_FP32)
+    assert (tri32.cpu().numpy() != want).mean() < 2e-3     # no FP64 re-trace on this entry point
+    assert (want >= 0).mean() > 0.99                       # closed room: a line always hits something
+
+
+# ------------------------------------------------------------------ check 2
+def _signature_match(rec, ref):
+    same = (rec["tri"] == ref["tri"]) & (rec["lobe"] == ref["lobe"]) & (rec["occ"] == ref["occ"]) & (rec["leak"] == ref["leak"])
+    # a path-bounce only counts as matching if the whole history up to it matches
+    return np.logical_and.accumulate(same, axis=2)
+
+
+def test_paths_fp64_mode_matches_reference_golden(rnd):
+    gold = g("cornell_paths_40.npz")
+    spp, nb, seed = int(gold["spp"]), int(gold["bounces"]), int(gold["seed"])
+    accum, rec = rnd.trace_paths(spp, nb, seed=seed, precision=ptb.PREC_FP64, records=True)
+    rec = {k: v.cpu().numpy() for k, v in rec.items()}
+    for k in ("tri", "lobe", "occ", "leak"):
+        assert np.array_equal(rec[k], gold[k]), k
+    assert np.abs(rec["contrib64"] - gold["contrib"]).max() < 1e-9
+    assert np.abs(rec["k_after64"] - gold["k_after"]).max() < 1e-9
+    rad = accum[:, :3].cpu().numpy() / spp
+    assert np.abs(rad - gold["radiance"]).max() < 1e-5     # accumulation buffer is float32
+
+
+def test_paths_fp32_mode_within_tolerance_of_reference_golden(rnd):
+    gold = g("cornell_paths_40.npz")
+    spp, nb, seed = int(gold["spp"]), int(gold["bounces"]), int(gold["seed"])
+    accum, rec = rnd.trace_paths(spp, nb, seed=seed, records=True)
+    rec = {k: v.cpu().numpy() for k, v in rec.items()}
+    ok = _signature_match(rec, gold)
+    live = gold["tri"] > -2
+    divergent = (~ok & live).sum() / live.sum()
+    assert divergent < 2e-3, divergent
+    err = np.abs(rec["contrib"] - gold["contrib"])
+    tol = ATOL + RTOL * np.abs(gold["contrib"])
+    assert (err <= tol)[ok].all()
+    assert np.all(np.abs(rec["k_after"] - gold["k_after"])[ok] <= ATOL + RTOL * np.abs(gold["k_after"][ok]))
+
+
+@pytest.mark.parametrize("res,spp,nb", [(96, 4, 4), (256, 2, 3)])
+def test_paths_vs_c_oracle_larger(rnd, flat, res, spp, nb):
+    orc = oracle.Oracle(flat, res, res)
+    ref = orc.trace(spp, nb, 1234)
+    rnd.counters(reset=True)
+    # FP64 mode: identical discrete history (transcendentals may differ by an ulp -> allow 20 ppm)
+    _, rec = rnd.trace_paths(spp, nb, seed=1234, width=res, height=res, precision=ptb.PREC_FP64, records=True)
+    rec = {k: v.cpu().numpy() for k, v in rec.items()}
+    live = ref["tri"] > -2
+    ok = _signature_match(rec, ref)
+    assert (~ok & live).sum() / live.sum() < 2e-5
+    assert np.abs(rec["contrib64"] - ref["contrib"])[ok].max() < 1e-9
+    # FP32 mode
+    accum, rec = rnd.trace_paths(spp, nb, seed=1234, width=res, height=res, records=True)
+    rec = {k: v.cpu().numpy() for k, v in rec.items()}
+    ok = _signature_match(rec, ref)
+    divergent = (~ok & live).sum() / live.sum()
+    assert divergent < 1e-3, divergent
+    assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
+    # counters agree with the oracle's ray census up to the divergent paths
+    c = rnd.counters(reset=True)
+    assert abs(c["closest_rays"] / 2 - ref["closest_rays"]) <= 0.01 * ref["closest_rays"]
+
+
+# ------------------------------------------------------------------ check 3
+def test_image_matches_make_image(rnd, flat):
+    gold = g("cornell_paths_40.npz")
+    spp, nb, seed = int(gold["spp"]), int(gold["bounces"]), int(gold["seed"])
+    accum, _ = rnd.trace_paths(spp, nb, seed=seed)
+    img = rnd.image(accum).cpu().numpy()
+    rad = accum[:, :3].cpu().numpy().astype(np.float64) / accum[:, 3:4].cpu().numpy().astype(np.float64)
+    assert np.array_equal(img, oracle.Oracle(flat).make_image(rad))          # same radiance -> same u8, exactly
+    diff = np.abs(img.astype(int) - gold["image"].astype(int))
+    assert (diff <= 1).mean() >= 0.99                                        # vs the reference's own image
+    kat = g("kat_misc.npz")
+    acc = np.concatenate([kat["img_radiance"], np.ones((576, 1))], 1).astype(np.float32)
+    import torch
+    got = rnd.image(torch.as_tensor(acc, device="cuda:0"), 24, 24).cpu().numpy()
+    assert (np.abs(got.astype(int) - kat["img_u8"].astype(int)) <= 1).mean() >= 0.995
+
+
+def test_converged_image_rmse(rnd, flat):
+    res, spp, nb = 64, 64, 3
+    ref = oracle.Oracle(flat, res, res).trace(spp, nb, 9, details=False)["radiance"]
+    accum, _ = rnd.trace_paths(spp, nb, seed=9, width=res, height=res)
+    rad = accum[:, :3].cpu().numpy() / spp
+    rmse = np.sqrt(np.mean((rad - ref) ** 2))
+    assert rmse <= 0.01 * np.abs(ref).mean(), rmse                           # stated tolerance: 1 % of mean
+
+
+# ------------------------------------------------------------------ properties
+def test_shards_partition_the_frame_bitwise(rnd):
+    import torch
+    res, spp, nb = 128, 3, 3
+    full, _ = rnd.trace_paths(spp, nb, seed=7, width=res, height=res)
+    merged = torch.zeros_like(full)
+    for s in range(3):
+        part, _ = rnd.trace_paths(spp, nb, seed=7, width=res, height=res, shard=s, n_shards=3, tile=100)
+        px, _ = rnd.pixels(res, res, s, 3, 100)
+        rnd.scatter(px, part, merged)
+    assert torch.equal(full, merged)
+
+
+def test_sample_ranges_and_batches_compose(rnd):
+    import torch
+    res, nb = 64, 3
+    a, _ = rnd.trace_paths(6, nb, seed=3, width=res, height=res)
+    b, _ = rnd.trace_paths(6, nb, seed=3, width=res, height=res, samples_per_batch=2)
+    assert torch.equal(a, b)                               # batching does not change any sample
+    c, _ = rnd.trace_paths(4, nb, seed=3, width=res, height=res)
+    c, _ = rnd.trace_paths(2, nb, seed=3, width=res, height=res, sample_begin=4, accum=c)
+    assert torch.allclose(a, c, rtol=1e-6, atol=1e-6)
+    assert float(a[:, 3].min()) == 6.0
+
+
+def test_render_drop_in(tmp_path):
+    im = ptb.render(ptb.CORNELL_SDL, n_rays=2, n_bounces=2)
+    assert im.size == (40, 40) and im.mode == "RGB"
+    im.save(str(tmp_path / "out.png"))
+    a = np.asarray(im)
+    assert a.max() == 255 and a.min() == 0
+
+
+def test_errors_are_loud(rnd):
+    with pytest.raises(ptb.PtbError):
+        rnd.trace_paths(1, 1, shard=5, n_shards=2)
+    r2 = ptb.Renderer(ptb.CORNELL_SDL, device=0, workspace_bytes=1024)
+    with pytest.raises(ptb.PtbError, match="workspace too small"):
+        r2.trace_paths(1, 1)
+    r2.close()
