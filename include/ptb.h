@@ -144,6 +144,19 @@ int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_
 /* scatter a shard's accumulation buffer (pixel-slot order) into a full-frame buffer (ray-index order) */
 int ptb_scatter_accum(const ptb_pixels *px, const float *d_accum_shard, float *d_accum_full, void *stream);
 
+/* Per-kernel-class device timing (CUDA events on the launch stream), for the roofline report.
+ * kinds: 0 camera rays, 1 closest-hit, 2 FP64 re-trace, 3 shade/bounce, 4 shadow/any-hit + NEE,
+ * 5 batch reduce, 6 tone map, 7 other, 8 LBVH build.  ptb_profile_read synchronises the device,
+ * writes the accumulated milliseconds and launch counts per kind (arrays of PTB_PROF_KINDS) and
+ * clears the accumulators. */
+#define PTB_PROF_KINDS 9
+int ptb_profile_enable(int on);
+int ptb_profile_read(double *ms_per_kind, uint64_t *launches_per_kind);
+
+/* FP32 FMA issue peak of the current device, measured with a register-resident FMA microbenchmark
+ * (roofline denominator for the compute-bound small-scene kernels). */
+int ptb_fp32_peak(double *tflops, void *stream);
+
 int ptb_counters_read(const ptb_scene *scene, ptb_counters *out, void *stream); /* synchronises stream */
 int ptb_counters_reset(const ptb_scene *scene, void *stream);
 int64_t ptb_pixel_count(const ptb_pixels *px);

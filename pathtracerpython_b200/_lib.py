@@ -12,7 +12,8 @@ FLAG_NO_FP64_RETRACE, FLAG_SHARE_PRIMARY = 1, 2
 
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
-           "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count"]
+           "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
+           "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak"]
 
 
 class PtbError(RuntimeError):
@@ -47,6 +48,8 @@ class Counters(C.Structure):
                                           "nodes_visited", "tris_tested")]
 
 
+PROF_KINDS = ["camera", "closest_hit", "fp64_retrace", "shade", "shadow", "reduce", "tonemap", "other", "bvh_build"]
+
 _lib = None
 
 
@@ -75,6 +78,9 @@ def lib():
         L.ptb_counters_read.argtypes = [C.c_void_p, C.POINTER(Counters), C.c_void_p]
         L.ptb_counters_reset.argtypes = [C.c_void_p, C.c_void_p]
         L.ptb_pixel_count.argtypes = [C.POINTER(Pixels)]
+        L.ptb_profile_enable.argtypes = [C.c_int]
+        L.ptb_fp32_peak.argtypes = [C.POINTER(C.c_double), C.c_void_p]
+        L.ptb_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -82,3 +88,21 @@ def lib():
 def check(rc, what):
     if rc != 0:
         raise PtbError(f"{what} failed ({rc}): {lib().ptb_last_error().decode()}")
+
+
+def profile_enable(on=True):
+    check(lib().ptb_profile_enable(1 if on else 0), "ptb_profile_enable")
+
+
+def profile_read():
+    """-> {kind: (milliseconds, launches)} accumulated since the last read (synchronises the device)."""
+    ms = (C.c_double * len(PROF_KINDS))()
+    n = (C.c_uint64 * len(PROF_KINDS))()
+    check(lib().ptb_profile_read(ms, n), "ptb_profile_read")
+    return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(PROF_KINDS)}
+
+
+def fp32_peak_tflops():
+    v = C.c_double()
+    check(lib().ptb_fp32_peak(C.byref(v), None), "ptb_fp32_peak")
+    return float(v.value)

@@ -38,9 +38,44 @@ static int grid_for(size_t work, int threads, int blocks_per_sm) {
     return (int)std::max<size_t>(1, std::min(need, cap));
 }
 
+// ---- optional per-kernel-class timing with CUDA events on the launch stream
+enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD };
+struct ProfRec { int kind; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::vector<cudaEvent_t> g_event_pool;
+static cudaEvent_t prof_event() {
+    cudaEvent_t e;
+    if (!g_event_pool.empty()) { e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    cudaEventCreate(&e);
+    return e;
+}
+struct ProfScope {
+    bool on; ProfRec r; cudaStream_t st;
+    ProfScope(int kind, cudaStream_t s) : on(g_prof_on), st(s) {
+        if (on) { r.kind = kind; r.a = prof_event(); r.b = prof_event(); cudaEventRecord(r.a, st); }
+    }
+    ~ProfScope() { if (on) { cudaEventRecord(r.b, st); g_prof.push_back(r); } }
+};
+
 }  // namespace ptb
 
 using namespace ptb;
+
+extern "C" int ptb_profile_enable(int on) { g_prof_on = on != 0; return PTB_OK; }
+extern "C" int ptb_profile_read(double *ms, uint64_t *launches) {
+    PTB_CUDA(cudaDeviceSynchronize());
+    for (int i = 0; i < PTB_PROF_KINDS; ++i) { if (ms) ms[i] = 0.0; if (launches) launches[i] = 0; }
+    for (ProfRec &r : g_prof) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, r.a, r.b);
+        if (ms) ms[r.kind] += t;
+        if (launches) launches[r.kind] += 1;
+        g_event_pool.push_back(r.a); g_event_pool.push_back(r.b);
+    }
+    g_prof.clear();
+    return PTB_OK;
+}
 
 struct ptb_scene {
     DScene d;                       // device view handed to kernels by value

@@ -69,6 +69,7 @@ static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
                             bool track, float *hit_t, int *hit_tri, cudaStream_t st) {
     const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
+    ProfScope ps_(PK_CLOSEST, st);
     if (track)
         k_closest_brute32<true><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
     else
@@ -92,22 +93,32 @@ extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32
     if (precision == PTB_PREC_FP32) {
         Queues<float> q;
         if (!queue_carve<float>(d_ws, ws_bytes, n, 1, q)) { set_error("workspace too small: need %zu bytes", queue_bytes<float>(n, 1)); return PTB_ERR_NOMEM; }
+        { ProfScope ps_(PK_GEN, st);
         k_gen<float><<<grid_for(n, 256, 8), 256, 0, st>>>(s->d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, 3);
+        }
         PTB_LAUNCHED();
         const bool track = !(flags & PTB_FLAG_NO_FP64_RETRACE);
         if ((rc = launch_closest32(s, q, 0, q.count, n, track, d_t, d_tri, st))) return rc;
         if (track) {
+            { ProfScope ps_(PK_RETRACE, st);
             k_retrace64<<<grid_for(n / 8 + 1, 128, 4), 128, 0, st>>>(s->d, bi.pm, bi.npix, q.unc_count, q.unc_list, d_t, d_tri);
+            }
             PTB_LAUNCHED();
         }
     } else if (precision == PTB_PREC_FP64) {
         Queues<double> q;
         if (!queue_carve<double>(d_ws, ws_bytes, n, 1, q)) { set_error("workspace too small: need %zu bytes", queue_bytes<double>(n, 1)); return PTB_ERR_NOMEM; }
+        { ProfScope ps_(PK_GEN, st);
         k_gen<double><<<grid_for(n, 256, 8), 256, 0, st>>>(s->d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, 3);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_CLOSEST, st);
         k_closest_brute64<<<grid_for(n, 128, 8), 128, 0, st>>>(s->d, q.qo[0], q.qd[0], q.count, q.hit_t, d_tri);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_OTHER, st);
         k_cvt_d2f<<<grid_for(n, 256, 8), 256, 0, st>>>(q.hit_t, d_t, (long long)n);
+        }
         PTB_LAUNCHED();
     } else { set_error("unknown precision %d", precision); return PTB_ERR_ARG; }
     return PTB_OK;
@@ -127,16 +138,22 @@ extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t
     unsigned *cnt = (unsigned *)(scratch + 2 * v * (size_t)n);
     if (precision == PTB_PREC_FP32) {
         float4 *qo = (float4 *)scratch, *qd = qo + n;
+        { ProfScope ps_(PK_OTHER, st);
         k_rays_to_queue32<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float *)d_rays, n, qo, qd, cnt);
+        }
         PTB_LAUNCHED();
         Queues<float> q; memset(&q, 0, sizeof(q));
         q.qo[0] = qo; q.qd[0] = qd;
         if ((rc = launch_closest32(s, q, 0, cnt, (size_t)n, false, (float *)d_t, d_tri, st))) return rc;
     } else {
         double4 *qo = (double4 *)scratch, *qd = qo + n;
+        { ProfScope ps_(PK_OTHER, st);
         k_rays_to_queue64<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const double *)d_rays, n, qo, qd, cnt);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_CLOSEST, st);
         k_closest_brute64<<<grid_for((size_t)n, 128, 8), 128, 0, st>>>(s->d, qo, qd, cnt, (double *)d_t, d_tri);
+        }
         PTB_LAUNCHED();
     }
     PTB_CUDA(cudaFreeAsync(scratch, st));
@@ -166,7 +183,9 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
     int rc;
     const size_t N = (size_t)bi.npix * bi.S;
     const DScene &d = s->d;
+    { ProfScope ps_(PK_GEN, st);
     k_gen<float><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
+    }
     PTB_LAUNCHED();
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
@@ -174,18 +193,26 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         const bool track = (b == 0) && !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
         if ((rc = launch_closest32(s, q, in, q.count + b, N, track, q.hit_t, q.hit_tri, st))) return rc;
         if (track) {
+            { ProfScope ps_(PK_RETRACE, st);
             k_retrace64<<<grid_for(N / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
+            }
             PTB_LAUNCHED();
         }
+        { ProfScope ps_(PK_SHADE, st);
         k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
             q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_SHADOW, st);
         k_shadow_brute32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem_tris(d.n_tri_obj), st>>>(
             d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        }
         PTB_LAUNCHED();
     }
+    { ProfScope ps_(PK_REDUCE, st);
     k_reduce<float><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+    }
     PTB_LAUNCHED();
     return PTB_OK;
 }
@@ -195,21 +222,31 @@ static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<do
                        float4 *accum, cudaStream_t st) {
     const size_t N = (size_t)bi.npix * bi.S;
     const DScene &d = s->d;
+    { ProfScope ps_(PK_GEN, st);
     k_gen<double><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
+    }
     PTB_LAUNCHED();
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
+        { ProfScope ps_(PK_CLOSEST, st);
         k_closest_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_SHADE, st);
         k_shade64<<<grid_for(N, PTB_SHADE_THREADS, 4), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out], q.sh_p, q.sh_d,
             q.sh_aux, q.L, q.cap, rec);
+        }
         PTB_LAUNCHED();
+        { ProfScope ps_(PK_SHADOW, st);
         k_shadow_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        }
         PTB_LAUNCHED();
     }
+    { ProfScope ps_(PK_REDUCE, st);
     k_reduce<double><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+    }
     PTB_LAUNCHED();
     return PTB_OK;
 }
@@ -252,7 +289,9 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
     RecPtrs rec = make_rec(records, npix, n_samples, p->bounces);
     if (rec.any) {
         const size_t n = (size_t)npix * n_samples * p->bounces;
+        { ProfScope ps_(PK_OTHER, st);
         k_init_records<<<grid_for(n, 256, 8), 256, 0, st>>>(rec, n);
+        }
         PTB_LAUNCHED();
     }
     BatchInfo bi;
@@ -275,11 +314,17 @@ extern "C" int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, 
     cudaStream_t st = (cudaStream_t)stream;
     unsigned long long *mm = (unsigned long long *)d_ws;
     const int n = width * height;
+    { ProfScope ps_(PK_TONEMAP, st);
     k_minmax_init<<<1, 1, 0, st>>>(mm);
+    }
     PTB_LAUNCHED();
+    { ProfScope ps_(PK_TONEMAP, st);
     k_minmax<<<grid_for((size_t)n, 256, 4), 256, 0, st>>>((const float4 *)d_accum, n, mm);
+    }
     PTB_LAUNCHED();
+    { ProfScope ps_(PK_TONEMAP, st);
     k_quantise<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float4 *)d_accum, width, height, mm, d_rgb);
+    }
     PTB_LAUNCHED();
     return PTB_OK;
 }
@@ -290,7 +335,10 @@ extern "C" int ptb_scatter_accum(const ptb_pixels *px, const float *d_src, float
     if (!d_src || !d_dst) { set_error("ptb_scatter_accum: null pointer"); return PTB_ERR_ARG; }
     PixelMap pm = make_pixel_map(px);
     if (pm.n == 0) return PTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    { ProfScope ps_(PK_OTHER, st);
     k_scatter_accum<<<grid_for((size_t)pm.n, 256, 8), 256, 0, (cudaStream_t)stream>>>(pm, (const float4 *)d_src, (float4 *)d_dst);
+    }
     PTB_LAUNCHED();
     return PTB_OK;
 }
@@ -313,5 +361,43 @@ extern "C" int ptb_counters_reset(const ptb_scene *s, void *stream) {
     if ((rc = check_scene(s))) return rc;
     PTB_CUDA(cudaMemsetAsync(s->d.counters, 0, CTR_COUNT * sizeof(unsigned long long), (cudaStream_t)stream));
     g_launches = 0;
+    return PTB_OK;
+}
+
+// ---------------------------------------------------------------- FP32 FMA peak microbenchmark
+namespace ptb {
+__global__ void __launch_bounds__(256) k_fma_peak(float *out, float a, float b, int iters) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; ++i) {
+        x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+        x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+    if (x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 == 12345.678f) out[0] = x0;
+}
+}  // namespace ptb
+
+extern "C" int ptb_fp32_peak(double *tflops, void *stream) {
+    if (!tflops) { set_error("ptb_fp32_peak: null"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    float *out = nullptr;
+    PTB_CUDA(cudaMalloc(&out, 16));
+    const int grid = num_sms() * 8, iters = 1 << 15;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(a, st);
+        k_fma_peak<<<grid, 256, 0, st>>>(out, 0.999f, 0.001f, iters);
+        cudaEventRecord(b, st);
+        PTB_CUDA(cudaEventSynchronize(b));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        const double fl = 2.0 * 8.0 * iters * 256.0 * grid;
+        if (rep > 0) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    cudaFree(out);
+    PTB_LAUNCHED();
+    *tflops = best;
     return PTB_OK;
 }
