@@ -8,6 +8,7 @@
 
 #include "ptb_image.cuh"
 #include "ptb_shade64.cuh"
+#include "ptb_planes.cuh"
 
 namespace ptb {
 
@@ -84,6 +85,8 @@ struct ptb_scene {
     float dt_scale;                 // FP32 error scale of the ray parameter (see ptb_isect.cuh)
     double build_ms;
     int n_nodes;
+    PlaneScene planes;              // plane-grouped records (brute-force scenes)
+    bool use_planes;
 };
 
 template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, const T **out, cudaStream_t st) {
@@ -123,6 +126,56 @@ static TriRec make_trirec(const double *v, int obj, double scale) {
     r.q2 = make_float4((float)mv[0], (float)mv[1], (float)mv[2], (float)(-dot_h(A, mv)));
     r.q3 = make_float4((float)(32.0 * 5.9604644775390625e-08 * scale * g), 0.f, bits_f(obj), 0.f);
     return r;
+}
+
+// Group the triangles of a small scene by supporting plane (ptb_planes.cuh).  Groups are ordered by
+// their lowest reference index, triangles inside a group keep reference order (object triangles before
+// light triangles because the light mesh is last).
+static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<TriRec> &tri, std::vector<PlaneRec> &planes,
+                               int &n_occ) {
+    const int n = desc->n_tri;
+    struct G { double n[3], d; std::vector<int> tris; };
+    std::vector<G> groups;
+    double scale = 1.0;
+    for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
+    for (int i = 0; i < n; ++i) {
+        const double *A = desc->verts + 9 * (size_t)i, *B = A + 3, *C = A + 6;
+        double ab[3], cb[3], nn[3];
+        for (int k = 0; k < 3; ++k) { ab[k] = A[k] - B[k]; cb[k] = C[k] - B[k]; }
+        cross_h(ab, cb, nn);
+        double nl = sqrt(dot_h(nn, nn));
+        int big = 0;
+        for (int k = 1; k < 3; ++k) if (fabs(nn[k]) > fabs(nn[big])) big = k;
+        double sgn = nn[big] < 0 ? -1.0 : 1.0;
+        for (int k = 0; k < 3; ++k) nn[k] = sgn * nn[k] / nl;
+        double d = dot_h(nn, A);
+        int found = -1;
+        // pair only triangles of the same set (object / light) so a group is wholly in or out of the occlusion set
+        if (nl > 0 && nl == nl)
+            for (size_t g = 0; g < groups.size(); ++g) {
+                const G &q = groups[g];
+                if (q.tris.size() < 2 && ((q.tris[0] < desc->n_tri_obj) == (i < desc->n_tri_obj)) &&
+                    fabs(q.n[0] - nn[0]) < 1e-10 && fabs(q.n[1] - nn[1]) < 1e-10 && fabs(q.n[2] - nn[2]) < 1e-10 &&
+                    fabs(q.d - d) < 1e-10 * scale) { found = (int)g; break; }
+            }
+        if (found < 0) { G q; q.n[0] = nn[0]; q.n[1] = nn[1]; q.n[2] = nn[2]; q.d = d; groups.push_back(q); found = (int)groups.size() - 1; }
+        groups[found].tris.push_back(i);
+    }
+    // groups are created in order of their first triangle => object groups precede light groups
+    n_occ = 0;
+    for (const G &q : groups) {
+        PlaneRec pr;
+        const int ta = q.tris[0], tb = q.tris.size() > 1 ? q.tris[1] : -1;
+        // the plane stored is triangle A's own (FP32-rounded) plane so a single-triangle group is exactly TriRec
+        pr.nd = tri[ta].q0;
+        pr.a1 = tri[ta].q1; pr.a2 = tri[ta].q2;
+        if (tb >= 0) { pr.b1 = tri[tb].q1; pr.b2 = tri[tb].q2; }
+        else { pr.b1 = make_float4(0.f, 0.f, 0.f, -1.f); pr.b2 = make_float4(0.f, 0.f, 0.f, -1.f); }
+        pr.ref_a = ta; pr.ref_b = tb; pr.min_ref = ta;
+        pr.n_obj = ta < desc->n_tri_obj ? (tb >= 0 ? 2 : 1) : 0;
+        if (pr.n_obj) n_occ++;
+        planes.push_back(pr);
+    }
 }
 
 extern "C" const char *ptb_last_error(void) { return g_err; }
@@ -182,13 +235,15 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     }
     std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
+    std::vector<PlaneRec> planes; int n_occ = 0;
+    build_plane_groups(desc, tri, planes, n_occ);
 
     DScene &d = s->d;
     int rc = PTB_OK;
     if ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
         (rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) || (rc = upload(s, verts, &d.verts64, st)) ||
         (rc = upload(s, normals, &d.normals64, st)) || (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
-        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
+        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
     }
@@ -198,6 +253,8 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     for (int i = 0; i < 4; ++i) d.ortho[i] = desc->ortho[i];
     d.ambient = desc->ambient;
     d.light_total = total;
+    s->planes.n_planes = (int)planes.size(); s->planes.n_occ = n_occ;
+    s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
     s->build_ms = 0.0;
     s->n_nodes = 0;
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope

@@ -70,7 +70,9 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
                             bool track, float *hit_t, int *hit_tri, cudaStream_t st) {
     const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
     ProfScope ps_(PK_CLOSEST, st);
-    if (track)
+    if (!track && s->use_planes)
+        k_closest_planes32<<<grid, PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(s->d, s->planes, q.qo[in], q.qd[in], d_count, hit_t, hit_tri);
+    else if (track)
         k_closest_brute32<true><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
     else
         k_closest_brute32<false><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
@@ -205,8 +207,12 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         }
         PTB_LAUNCHED();
         { ProfScope ps_(PK_SHADOW, st);
-        k_shadow_brute32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem_tris(d.n_tri_obj), st>>>(
-            d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        if (s->use_planes)
+            k_shadow_planes32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(
+                d, s->planes, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        else
+            k_shadow_brute32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem_tris(d.n_tri_obj), st>>>(
+                d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
         }
         PTB_LAUNCHED();
     }

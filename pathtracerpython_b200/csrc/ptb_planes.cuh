@@ -1,0 +1,170 @@
+// ptb_planes.cuh - plane-grouped brute-force traversal (small scenes, FP32 product path).
+//
+// Meshes of walls and boxes are made of coplanar triangle groups (every Cornell quad is 2 triangles in
+// one plane).  The ray/plane part of utils.py:116-120 (n.d, n.o, t, P) depends only on the plane, so it is
+// evaluated once per group; only the inside test (utils.py:72-91) runs per triangle.  A warp vote skips
+// a group when no lane can use it (plane farther than the lane's current best / outside the shadow
+// range / sample already occluded).  For shadow rays the 3 light samples of a path share the origin, so
+// n.o is evaluated once per plane and path.  Decisions are the same FP32 decisions as the per-triangle
+// kernels up to rounding; bit-exact primary ids still come from the tracked kernel + FP64 re-trace.
+#pragma once
+#include "ptb_shadow.cuh"
+
+namespace ptb {
+
+struct PlaneRec {      // 96 B = 6 x float4: one supporting plane + up to two of its triangles
+    float4 nd;         // unit normal, d0
+    float4 a1, a2;     // triangle A barycentric gradients (TriRec q1, q2)
+    float4 b1, b2;     // triangle B (or a never-inside dummy: u == -1)
+    int ref_a, ref_b;  // reference triangle indices (ref_b = -1 for the dummy)
+    int n_obj;         // how many of (A, B) belong to the occlusion set: 0, 1 (A only) or 2
+    int min_ref;       // == ref_a
+};
+struct PlaneScene {    // device pointer, small; staged into shared memory by every block
+    const PlaneRec *planes;   // groups with n_obj > 0 first (n_occ of them), light-only groups last
+    int n_planes, n_occ;
+};
+
+__host__ __device__ inline size_t plane_smem_bytes(int n_planes) { return (size_t)n_planes * sizeof(PlaneRec) + 16; }
+__device__ __forceinline__ const PlaneRec *stage_planes(unsigned char *smem, const PlaneScene &ps) {
+    const float4 *a = reinterpret_cast<const float4 *>(ps.planes);
+    float4 *da = reinterpret_cast<float4 *>(smem);
+    for (int i = threadIdx.x; i < ps.n_planes * 6; i += blockDim.x) da[i] = __ldg(a + i);
+    __syncthreads();
+    return reinterpret_cast<const PlaneRec *>(smem);
+}
+
+__device__ __forceinline__ float bary_min(const float4 q1, const float4 q2, float px, float py, float pz) {
+    const float u = fmaf(q1.z, pz, fmaf(q1.y, py, fmaf(q1.x, px, q1.w)));
+    const float v = fmaf(q2.z, pz, fmaf(q2.y, py, fmaf(q2.x, px, q2.w)));
+    return fminf(fminf(u, v), 1.0f - u - v);
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+#define PTB_TMIN_F 3.1622776e-3f   // sqrt(1e-5): |t| threshold equivalent to squared_dist > ZERO
+
+// ---------------------------------------------------------------- closest hit
+__global__ void __launch_bounds__(PTB_TRACE_THREADS)
+k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
+                   const unsigned *__restrict__ d_count, float *__restrict__ hit_t, int *__restrict__ hit_tri) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const PlaneRec *planes = stage_planes(smem_raw, ps);
+    const unsigned count = *d_count;
+    const unsigned stride = gridDim.x * blockDim.x;
+    // whole warps iterate together so the votes below are legal
+    const unsigned count_w = (count + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count_w; i += stride) {
+        const bool live = i < count;
+        const float4 a = live ? qo[i] : make_float4(0, 0, 0, 0), b = live ? qd[i] : make_float4(1, 0, 0, 0);
+        float best_a = live ? 3.0e38f : 0.f, best_t = 0.f;
+        int best_ref = -1;
+        for (int g = 0; g < ps.n_planes; ++g) {
+            const float4 nd = planes[g].nd;
+            const float dn = fmaf(nd.z, b.z, fmaf(nd.y, b.y, nd.x * b.x));
+            const float on = nd.w - fmaf(nd.z, a.z, fmaf(nd.y, a.y, nd.x * a.x));
+            const float t = on * rcp_approx(dn);
+            const float at = fabsf(t);
+            const bool ok = (fabsf(dn) > PTB_ZERO_F) && (at > PTB_TMIN_F) && (at < best_a);
+            if (!__any_sync(0xffffffffu, ok)) continue;
+            const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
+            const float ma = bary_min(planes[g].a1, planes[g].a2, px, py, pz);
+            const float mb = bary_min(planes[g].b1, planes[g].b2, px, py, pz);
+            // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
+            const bool ha = ok && ma > 0.0f, hb = ok && mb > 0.0f;
+            if (ha || hb) { best_a = at; best_t = t; best_ref = ha ? planes[g].ref_a : planes[g].ref_b; }
+        }
+        if (live) {
+            hit_t[i] = best_t;
+            hit_tri[i] = best_ref;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sc.counters + CTR_CLOSEST, (unsigned long long)count);
+}
+
+// ---------------------------------------------------------------- shadow rays + NEE accumulation
+__global__ void __launch_bounds__(PTB_TRACE_THREADS)
+k_shadow_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d,
+                  const int2 *__restrict__ sh_aux, const unsigned *__restrict__ d_count, float4 *__restrict__ L,
+                  int cap, int bounce, RecPtrs rec) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const PlaneRec *planes = stage_planes(smem_raw, ps);
+    const unsigned count = *d_count;
+    const unsigned stride = gridDim.x * blockDim.x;
+    const unsigned count_w = (count + 31u) & ~31u;
+    const float lc0 = (float)sc.light_color[0], lc1 = (float)sc.light_color[1], lc2 = (float)sc.light_color[2];
+    const float ambient = (float)sc.ambient;
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < count_w; j += stride) {
+        const bool live = j < count;
+        const unsigned jj = live ? j : 0u;
+        const float4 pk = sh_p[jj];
+        const float4 d0 = sh_d[jj], d1 = sh_d[(size_t)cap + jj], d2 = sh_d[2 * (size_t)cap + jj];
+        bool occ0 = !live, occ1 = !live;       // dead lanes never keep a group alive
+        int leak_ref = live ? 0x7fffffff : -1; // lowest reference index among occluders of sample 2
+        for (int g = 0; g < ps.n_occ; ++g) {
+            const float4 nd = planes[g].nd;
+            const float on = nd.w - fmaf(nd.z, pk.z, fmaf(nd.y, pk.y, nd.x * pk.x));
+            const float dn0 = fmaf(nd.z, d0.z, fmaf(nd.y, d0.y, nd.x * d0.x));
+            const float dn1 = fmaf(nd.z, d1.z, fmaf(nd.y, d1.y, nd.x * d1.x));
+            const float dn2 = fmaf(nd.z, d2.z, fmaf(nd.y, d2.y, nd.x * d2.x));
+            const float t0 = on * rcp_approx(dn0), t1 = on * rcp_approx(dn1), t2 = on * rcp_approx(dn2);
+            const float s0 = t0 * t0, s1 = t1 * t1, s2 = t2 * t2;
+            // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
+            const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w);
+            const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w);
+            const bool ok2 = (planes[g].min_ref < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
+            if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
+            const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
+            const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);
+            const float p2x = fmaf(t2, d2.x, pk.x), p2y = fmaf(t2, d2.y, pk.y), p2z = fmaf(t2, d2.z, pk.z);
+            const float4 a1 = planes[g].a1, a2 = planes[g].a2;
+            const bool ha0 = bary_min(a1, a2, p0x, p0y, p0z) > 0.0f;
+            const bool ha1 = bary_min(a1, a2, p1x, p1y, p1z) > 0.0f;
+            const bool ha2 = bary_min(a1, a2, p2x, p2y, p2z) > 0.0f;
+            bool hb0 = false, hb1 = false, hb2 = false;
+            if (planes[g].n_obj > 1) {             // warp-uniform
+                const float4 b1 = planes[g].b1, b2 = planes[g].b2;
+                hb0 = bary_min(b1, b2, p0x, p0y, p0z) > 0.0f;
+                hb1 = bary_min(b1, b2, p1x, p1y, p1z) > 0.0f;
+                hb2 = bary_min(b1, b2, p2x, p2y, p2z) > 0.0f;
+            }
+            occ0 = occ0 || (ok0 && (ha0 || hb0));
+            occ1 = occ1 || (ok1 && (ha1 || hb1));
+            if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
+        }
+        if (!live) continue;
+        const int2 aux = sh_aux[j];
+        const float4 sn = __ldg(sc.tri_sn + aux.y);
+        const int obj = __float_as_int(sn.w);
+        const bool occ2 = leak_ref != 0x7fffffff;
+        const int leak = occ2 ? __float_as_int(__ldg(sc.tri_sn + leak_ref).w) : sc.n_obj - 1;
+        float dot_sum = 0.f;
+        if (!occ0) dot_sum += fmaf(d0.z, sn.z, fmaf(d0.y, sn.y, d0.x * sn.x));
+        if (!occ1) dot_sum += fmaf(d1.z, sn.z, fmaf(d1.y, sn.y, d1.x * sn.x));
+        if (!occ2) dot_sum += fmaf(d2.z, sn.z, fmaf(d2.y, sn.y, d2.x * sn.x));
+        const float dotv = dot_sum / 3.0f;
+        const float *m = sc.mat32 + 8 * obj, *lm = sc.mat32 + 8 * leak;
+        const float ka = __ldg(m + 3);
+        const float c0 = __ldg(m + 0) * ka * ambient + lc0 * __ldg(lm + 0) * dotv;
+        const float c1 = __ldg(m + 1) * ka * ambient + lc1 * __ldg(lm + 1) * dotv;
+        const float c2 = __ldg(m + 2) * ka * ambient + lc2 * __ldg(lm + 2) * dotv;
+        float4 l = L[aux.x];
+        l.x = fmaf(c0, pk.w, l.x); l.y = fmaf(c1, pk.w, l.y); l.z = fmaf(c2, pk.w, l.z);
+        L[aux.x] = l;
+        if (rec.any) {
+            const size_t ri = rec.index(aux.x, bounce);
+            if (rec.occ) rec.occ[ri] = (int8_t)((occ0 ? 1 : 0) | (occ1 ? 2 : 0) | (occ2 ? 4 : 0));
+            if (rec.leak) rec.leak[ri] = (int8_t)leak;
+            if (rec.contrib) { rec.contrib[3 * ri] = c0 * pk.w; rec.contrib[3 * ri + 1] = c1 * pk.w; rec.contrib[3 * ri + 2] = c2 * pk.w; }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(sc.counters + CTR_SHADOW, 3ull * count);
+        atomicAdd(sc.counters + CTR_SHADED, (unsigned long long)count);
+    }
+}
+
+}  // namespace ptb
