@@ -69,7 +69,8 @@ typedef struct {
 enum { PTB_PREC_FP32 = 0, PTB_PREC_FP64 = 1 };
 enum {
     PTB_FLAG_NO_FP64_RETRACE = 1,   /* FP32 only: skip the FP64 re-trace of uncertain primary hits */
-    PTB_FLAG_SHARE_PRIMARY = 2      /* trace the (identical, main.py:191) primary ray once per pixel */
+    PTB_FLAG_SHARE_PRIMARY = 2,     /* trace the (identical, main.py:191) primary ray once per pixel */
+    PTB_FLAG_COUNT_NODES = 4        /* instrumented run: count LBVH nodes visited / triangles tested */
 };
 
 typedef struct {

@@ -9,6 +9,8 @@
 #include "ptb_image.cuh"
 #include "ptb_shade64.cuh"
 #include "ptb_planes.cuh"
+#include "ptb_bvh_build.cuh"
+#include "ptb_bvh_kernels.cuh"
 
 namespace ptb {
 
@@ -86,6 +88,7 @@ struct ptb_scene {
     double build_ms;
     int n_nodes;
     PlaneScene planes;              // plane-grouped records (brute-force scenes)
+    float pad;                      // LBVH box inflation
     bool use_planes;
 };
 
@@ -178,6 +181,77 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
     }
 }
 
+// GPU LBVH build (ptb_bvh_build.cuh).  Temporary buffers are freed before returning; the handle keeps
+// the 64 B nodes, the leaf-ordered TriRec array and the slot -> reference index table.
+static int build_lbvh(ptb_scene *s, cudaStream_t st) {
+    DScene &d = s->d;
+    const int n = d.n_tri;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    Aabb *tri_box = nullptr, *node_box = nullptr; float4 *centroid = nullptr; unsigned *scene_box = nullptr, *keys[2] = {nullptr, nullptr};
+    int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
+    unsigned *ghist = nullptr, *flags = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
+    std::vector<void *> tmp;
+    auto alloc = [&](void **p, size_t bytes, bool keep) -> int {
+        PTB_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));
+        (keep ? s->allocs : tmp).push_back(*p);
+        return PTB_OK;
+    };
+    int rc;
+    if ((rc = alloc((void **)&tri_box, sizeof(Aabb) * n, false)) || (rc = alloc((void **)&node_box, sizeof(Aabb) * n, false)) ||
+        (rc = alloc((void **)&centroid, sizeof(float4) * n, false)) || (rc = alloc((void **)&scene_box, 64, false)) ||
+        (rc = alloc((void **)&keys[0], 4 * (size_t)n, false)) || (rc = alloc((void **)&keys[1], 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&vals[0], 4 * (size_t)n, false)) || (rc = alloc((void **)&vals[1], 4 * (size_t)n, true)) ||
+        (rc = alloc((void **)&parent_inner, 4 * (size_t)n, false)) || (rc = alloc((void **)&parent_leaf, 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&node_minref, 4 * (size_t)n, false)) || (rc = alloc((void **)&child, sizeof(int2) * n, false)) ||
+        (rc = alloc((void **)&ghist, 4 * (size_t)256 * n_tiles, false)) || (rc = alloc((void **)&flags, 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&nodes, sizeof(BvhNode) * (size_t)n, true)) || (rc = alloc((void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true))) {
+        for (void *p : tmp) cudaFree(p);
+        return rc;
+    }
+    cudaEventRecord(e0, st);
+    {
+        ProfScope ps_(PK_BUILD, st);
+        const int g = grid_for((size_t)n, 256, 8);
+        k_bounds_init<<<1, 32, 0, st>>>(scene_box);
+        k_tri_bounds<<<g, 256, 0, st>>>(d.verts64, n, tri_box, centroid, scene_box);
+        k_morton<<<g, 256, 0, st>>>(centroid, n, scene_box, keys[0], vals[0]);
+        g_launches += 3;
+        // 4 passes x 8 bits; after an even number of passes the result is back in buffer 0 -> copy into the kept buffer
+        int cur = 0;
+        const int rs_blocks = (n_tiles + RS_WARPS - 1) / RS_WARPS;
+        for (int pass = 0; pass < 4; ++pass) {
+            k_rs_hist<<<rs_blocks, RS_WARPS * 32, 0, st>>>(keys[cur], n, 8 * pass, n_tiles, ghist);
+            k_rs_scan<<<1, 1024, 0, st>>>(ghist, (size_t)256 * n_tiles);
+            k_rs_scatter<<<rs_blocks, RS_WARPS * 32, 0, st>>>(keys[cur], vals[cur], n, 8 * pass, n_tiles, ghist, keys[cur ^ 1], vals[cur ^ 1]);
+            g_launches += 3;
+            cur ^= 1;
+        }
+        cudaMemcpyAsync(vals[1], vals[0], 4 * (size_t)n, cudaMemcpyDeviceToDevice, st);   // cur == 0 after 4 passes
+        cudaMemsetAsync(flags, 0, 4 * (size_t)n, st);
+        k_karras<<<g, 256, 0, st>>>(keys[0], n, child, parent_inner, parent_leaf);
+        k_refit<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, parent_inner, parent_leaf, node_box, node_minref, flags);
+        k_pack<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, node_box, node_minref, s->pad, nodes);
+        k_gather_tris<<<g, 256, 0, st>>>(n, vals[1], d.tri, tri_sorted);
+        g_launches += 4;
+    }
+    cudaEventRecord(e1, st);
+    cudaError_t err = cudaStreamSynchronize(st);
+    if (err == cudaSuccess) err = cudaGetLastError();
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    for (void *p : tmp) cudaFree(p);
+    if (err != cudaSuccess) { set_error("LBVH build failed: %s", cudaGetErrorString(err)); return PTB_ERR_CUDA; }
+    d.nodes = nodes;
+    d.tri = tri_sorted;       // leaf order; the reference-order array stays allocated but unused
+    d.tri_id = vals[1];
+    s->build_ms = ms;
+    s->n_nodes = n - 1;
+    return PTB_OK;
+}
+
 extern "C" const char *ptb_last_error(void) { return g_err; }
 extern "C" int ptb_version(void) { return 100; }
 
@@ -196,7 +270,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         set_error("brute-force traversal holds at most %d triangles in shared memory", PTB_BRUTE_MAX_TRI);
         return PTB_ERR_UNSUPPORTED;
     }
-    if (accel != PTB_ACCEL_BRUTE) { set_error("LBVH traversal not built yet"); return PTB_ERR_UNSUPPORTED; }
+    if (accel == PTB_ACCEL_LBVH && desc->n_tri < 2) { set_error("LBVH needs at least 2 triangles"); return PTB_ERR_UNSUPPORTED; }
 
     ptb_scene *s = new ptb_scene();
     memset(&s->d, 0, sizeof(DScene));
@@ -213,6 +287,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     for (int i = 0; i < n; ++i) {
         if (tobj[i] < 0 || tobj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
         tri[i] = make_trirec(desc->verts + 9 * (size_t)i, tobj[i], scale);
+        tri[i].q3.w = bits_f(i);                     // reference index travels with the record (LBVH leaf order)
         const double *nn = desc->normals + 3 * (size_t)i;
         sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(tobj[i]));
         ids[i] = i;
@@ -236,7 +311,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<PlaneRec> planes; int n_occ = 0;
-    build_plane_groups(desc, tri, planes, n_occ);
+    if (accel == PTB_ACCEL_BRUTE) build_plane_groups(desc, tri, planes, n_occ);
 
     DScene &d = s->d;
     int rc = PTB_OK;
@@ -257,6 +332,8 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
     s->build_ms = 0.0;
     s->n_nodes = 0;
+    s->pad = (float)(scale * 3.814697265625e-06);   // 2^-18 * scene scale
+    if (accel == PTB_ACCEL_LBVH && (rc = build_lbvh(s, st))) { ptb_scene_destroy(s); return rc; }
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
     *out = s;
     return PTB_OK;

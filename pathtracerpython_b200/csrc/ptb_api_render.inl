@@ -13,7 +13,7 @@ k_retrace64(DScene sc, PixelMap pm, int npix, const unsigned *__restrict__ unc_c
         const int r = pm.ray_index(i % npix);
         d3 o, d;
         primary_ray64(sc, pm.W, pm.H, r, o, d);
-        const Hit64 h = closest_brute64(sc, o, d);
+        const Hit64 h = sc.accel == PTB_ACCEL_LBVH ? closest_bvh64(sc, o, d) : closest_brute64(sc, o, d);
         hit_tri[i] = h.tri;
         if (h.tri >= 0) {
             const d3 vr = xdiv3(d, xnorm(d));
@@ -64,18 +64,41 @@ static int check_pixels(const ptb_pixels *px) {
 }
 
 static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
+static bool g_count_nodes = false;   // instrumented (untimed) run: count nodes visited / triangles tested
 
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
                             bool track, float *hit_t, int *hit_tri, cudaStream_t st) {
-    const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
     ProfScope ps_(PK_CLOSEST, st);
+    if (s->d.accel == PTB_ACCEL_LBVH) {
+        const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
+        if (track)
+            k_closest_bvh32<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+        else if (g_count_nodes)
+            k_closest_bvh32<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+        else
+            k_closest_bvh32<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+        PTB_LAUNCHED();
+        return PTB_OK;
+    }
+    const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
     if (!track && s->use_planes)
         k_closest_planes32<<<grid, PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(s->d, s->planes, q.qo[in], q.qd[in], d_count, hit_t, hit_tri);
     else if (track)
         k_closest_brute32<true><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
     else
         k_closest_brute32<false><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+static int launch_closest64(const ptb_scene *s, const double4 *qo, const double4 *qd, const unsigned *d_count, size_t upper,
+                            double *hit_t, int *hit_tri, cudaStream_t st) {
+    ProfScope ps_(PK_CLOSEST, st);
+    if (s->d.accel == PTB_ACCEL_LBVH)
+        k_closest_bvh64<<<grid_for(upper, PTB_BVH_THREADS, 8), PTB_BVH_THREADS, 0, st>>>(s->d, qo, qd, d_count, hit_t, hit_tri);
+    else
+        k_closest_brute64<<<grid_for(upper, 128, 8), 128, 0, st>>>(s->d, qo, qd, d_count, hit_t, hit_tri);
     PTB_LAUNCHED();
     return PTB_OK;
 }
@@ -114,10 +137,7 @@ extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32
         k_gen<double><<<grid_for(n, 256, 8), 256, 0, st>>>(s->d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, 3);
         }
         PTB_LAUNCHED();
-        { ProfScope ps_(PK_CLOSEST, st);
-        k_closest_brute64<<<grid_for(n, 128, 8), 128, 0, st>>>(s->d, q.qo[0], q.qd[0], q.count, q.hit_t, d_tri);
-        }
-        PTB_LAUNCHED();
+        if ((rc = launch_closest64(s, q.qo[0], q.qd[0], q.count, n, q.hit_t, d_tri, st))) return rc;
         { ProfScope ps_(PK_OTHER, st);
         k_cvt_d2f<<<grid_for(n, 256, 8), 256, 0, st>>>(q.hit_t, d_t, (long long)n);
         }
@@ -153,10 +173,7 @@ extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t
         k_rays_to_queue64<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const double *)d_rays, n, qo, qd, cnt);
         }
         PTB_LAUNCHED();
-        { ProfScope ps_(PK_CLOSEST, st);
-        k_closest_brute64<<<grid_for((size_t)n, 128, 8), 128, 0, st>>>(s->d, qo, qd, cnt, (double *)d_t, d_tri);
-        }
-        PTB_LAUNCHED();
+        if ((rc = launch_closest64(s, qo, qd, cnt, (size_t)n, (double *)d_t, d_tri, st))) return rc;
     }
     PTB_CUDA(cudaFreeAsync(scratch, st));
     return PTB_OK;
@@ -207,7 +224,12 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         }
         PTB_LAUNCHED();
         { ProfScope ps_(PK_SHADOW, st);
-        if (s->use_planes)
+        if (d.accel == PTB_ACCEL_LBVH) {
+            if (g_count_nodes)
+                k_shadow_bvh32<true><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+            else
+                k_shadow_bvh32<false><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        } else if (s->use_planes)
             k_shadow_planes32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(
                 d, s->planes, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
         else
@@ -235,10 +257,7 @@ static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<do
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
-        { ProfScope ps_(PK_CLOSEST, st);
-        k_closest_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri);
-        }
-        PTB_LAUNCHED();
+        { int rc2 = launch_closest64(s, q.qo[in], q.qd[in], q.count + b, N, q.hit_t, q.hit_tri, st); if (rc2) return rc2; }
         { ProfScope ps_(PK_SHADE, st);
         k_shade64<<<grid_for(N, PTB_SHADE_THREADS, 4), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out], q.sh_p, q.sh_d,
@@ -246,7 +265,10 @@ static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<do
         }
         PTB_LAUNCHED();
         { ProfScope ps_(PK_SHADOW, st);
-        k_shadow_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        if (d.accel == PTB_ACCEL_LBVH)
+            k_shadow_bvh64<<<grid_for(N, PTB_BVH_THREADS, 8), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
+        else
+            k_shadow_brute64<<<grid_for(N, 128, 8), 128, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
         }
         PTB_LAUNCHED();
     }
@@ -293,6 +315,7 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         return PTB_ERR_NOMEM;
     }
     RecPtrs rec = make_rec(records, npix, n_samples, p->bounces);
+    g_count_nodes = (p->flags & PTB_FLAG_COUNT_NODES) != 0;
     if (rec.any) {
         const size_t n = (size_t)npix * n_samples * p->bounces;
         { ProfScope ps_(PK_OTHER, st);
