@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--spp", type=int, default=1024)
     ap.add_argument("--bounces", type=int, default=5)
     ap.add_argument("--scene", default=None)
+    ap.add_argument("--tess", type=int, default=0, help="tessellate every triangle into N x N (configs 4/5: 177 -> 1.0M, 559 -> 10.0M triangles)")
     ap.add_argument("--seed", type=int, default=9)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the bounded baseline sample")
@@ -43,7 +44,8 @@ def parse():
 
 
 def workload_name(a):
-    return f"cornell_box_{a.res}x{a.res}_{a.spp}spp_b{a.bounces}"
+    t = f"_tess{a.tess}_{32 * a.tess * a.tess}tri" if a.tess else ""
+    return f"cornell_box{t}_{a.res}x{a.res}_{a.spp}spp_b{a.bounces}"
 
 
 # ------------------------------------------------------------------ CPU baseline (oracle port, bounded sample)
@@ -53,9 +55,13 @@ def cpu_sample(a, seconds):
     import numpy as np
     from oracle import oracle, scene_port
     import pathtracerpython_b200 as ptb
-    flat = scene_port.load_scene(a.scene or ptb.CORNELL_SDL)
+    if a.tess:
+        from pathtracerpython_b200 import synth
+        flat = synth.tessellate(ptb.Scene(a.scene or ptb.CORNELL_SDL), a.tess).flatten()
+    else:
+        flat = scene_port.load_scene(a.scene or ptb.CORNELL_SDL)
     orc = oracle.Oracle(flat, a.res, a.res)
-    side = 64
+    side = 64 if not a.tess else 4
     lo = (a.res - side) // 2
     px = np.array([ix * a.res + iy for ix in range(lo, lo + side) for iy in range(lo, lo + side)], np.int64)
     t = time.perf_counter()
@@ -145,6 +151,9 @@ def run_ours(a):
         dist.init_process_group("nccl", device_id=dev)
     scene_path = a.scene or ptb.CORNELL_SDL
     scene = ptb.Scene(scene_path)
+    if a.tess:
+        from pathtracerpython_b200 import synth
+        scene = synth.tessellate(scene, a.tess)
     W = H = a.res
     r = ptb.Renderer(scene, device=local)
     px, _ = r.pixels(W, H, rank, world, H)                    # column-interleaved tiles
@@ -227,31 +236,58 @@ def run_ours(a):
     top = max(("closest_hit", "shadow", "shade"), key=lambda k: prof[k][0])
     n_tri, n_tri_obj = r.n_tri, int(flat["n_tri_obj"])
     t_top = prof[top][0] / 1e3
-    if top == "closest_hit":
-        flops = ctr["closest_rays"] * n_tri * F_TEST
-        bytes_ = ctr["closest_rays"] * RAY_STATE_BYTES["closest_hit"]
-    elif top == "shadow":
-        flops = ctr["shadow_rays"] * n_tri_obj * F_TEST     # upper bound: the walk stops at the first occluder
-        bytes_ = ctr["shaded"] * RAY_STATE_BYTES["shadow"]
+    info = r.info()
+    kernel_ms = {k: round(v[0], 3) for k, v in prof.items() if v[1]}
+    if info["accel"] == "lbvh":
+        # instrumented, untimed pass of the same kernels on the same LBVH: nodes fetched / triangles tested per ray
+        r.counters(reset=True)
+        r.trace_paths(1, a.bounces, seed=a.seed, width=W, height=H, shard=rank, n_shards=world, tile=H, flags=_lib.FLAG_COUNT_NODES)
+        ci = r.counters(reset=True)
+        n_ch, t_ch = ci["nodes_visited"] / max(1, ci["closest_rays"]), ci["tris_tested"] / max(1, ci["closest_rays"])
+        n_sh, t_sh = ci["nodes_visited_shadow"] / max(1, ci["shadow_rays"]), ci["tris_tested_shadow"] / max(1, ci["shadow_rays"])
+        if top == "shadow":
+            bytes_ = ctr["shadow_rays"] * (64 * n_sh + 64 * t_sh) + ctr["shaded"] * RAY_STATE_BYTES["shadow"]
+            flops = ctr["shadow_rays"] * (36 * n_sh + F_TEST * t_sh)
+        else:
+            top = "closest_hit"
+            t_top = prof[top][0] / 1e3
+            bytes_ = ctr["closest_rays"] * (RAY_STATE_BYTES["closest_hit"] + 64 * n_ch + 64 * t_ch)
+            flops = ctr["closest_rays"] * (36 * n_ch + F_TEST * t_ch)
+        roof = {"kernel": top, "bound": "hbm", "achieved": bytes_ / t_top / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": bytes_ / t_top / 1e9 / hbm_peak,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650",
+                "traffic": None,
+                "per_ray": {"nodes_closest": n_ch, "tris_closest": t_ch, "nodes_shadow": n_sh, "tris_shadow": t_sh},
+                "fp32": {"achieved": flops / t_top / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": flops / t_top / 1e12 / fp32_peak if fp32_peak else None},
+                "launches": prof[top][1], "avg_launch_ms": prof[top][0] / max(1, prof[top][1]), "kernel_ms": kernel_ms,
+                "note": "algorithmic bytes = 64 B per node fetched + 64 B per triangle record tested + ray/hit state (DESIGN.md)"}
     else:
-        flops = ctr["shaded"] * 400
-        bytes_ = ctr["closest_rays"] * RAY_STATE_BYTES["shade"]
-    roof = {"kernel": top, "bound": "fp32", "achieved": flops / t_top / 1e12 if t_top else None,
-            "peak": fp32_peak, "unit": "TFLOP/s",
-            "frac": (flops / t_top / 1e12 / fp32_peak) if (t_top and fp32_peak) else None,
-            "peak_source": "FP32 FMA microbenchmark run by this bench (ptb_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
-            "traffic": None,
-            "hbm": {"achieved": bytes_ / t_top / 1e9 if t_top else None, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": bytes_ / t_top / 1e9 / hbm_peak if t_top else None,
-                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650"},
-            "launches": prof[top][1], "avg_launch_ms": prof[top][0] / max(1, prof[top][1]),
-            "kernel_ms": {k: round(v[0], 3) for k, v in prof.items() if v[1]},
-            "note": "32-triangle scene lives in shared memory: the kernel is FP32-issue bound, not HBM bound (DESIGN.md)"}
+        if top == "closest_hit":
+            flops = ctr["closest_rays"] * n_tri * F_TEST
+            bytes_ = ctr["closest_rays"] * RAY_STATE_BYTES["closest_hit"]
+        elif top == "shadow":
+            flops = ctr["shadow_rays"] * n_tri_obj * F_TEST     # the per-triangle formulation's work
+            bytes_ = ctr["shaded"] * RAY_STATE_BYTES["shadow"]
+        else:
+            flops = ctr["shaded"] * 400
+            bytes_ = ctr["closest_rays"] * RAY_STATE_BYTES["shade"]
+        roof = {"kernel": top, "bound": "fp32", "achieved": flops / t_top / 1e12 if t_top else None,
+                "peak": fp32_peak, "unit": "TFLOP/s",
+                "frac": (flops / t_top / 1e12 / fp32_peak) if (t_top and fp32_peak) else None,
+                "peak_source": "FP32 FMA microbenchmark run by this bench (ptb_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
+                "traffic": None,
+                "hbm": {"achieved": bytes_ / t_top / 1e9 if t_top else None, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": bytes_ / t_top / 1e9 / hbm_peak if t_top else None,
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650"},
+                "launches": prof[top][1], "avg_launch_ms": prof[top][0] / max(1, prof[top][1]), "kernel_ms": kernel_ms,
+                "note": "scene lives in shared memory: the kernel is FP32-issue bound, not HBM bound (DESIGN.md)"}
     line = {
         "metric": "Msamples/s", "value": samples / sec / 1e6, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "scene": os.path.basename(scene_path), "triangles": n_tri,
+                   "accel": info["accel"], "bvh_build_ms": info["build_ms"],
                    "width": W, "height": H, "spp": a.spp, "bounces": a.bounces, "sharding": f"column-interleaved tiles x{world}",
                    "l2_policy": "inputs larger than L2 (wavefront state of one batch is GBs)"},
         "mrays_per_s": float(rays[0]) / sec / 1e6, "closest_mrays_per_s": float(rays[1]) / sec / 1e6,

@@ -105,8 +105,10 @@ typedef struct {
     uint64_t samples;        /* pixel samples started */
     uint64_t retraced;       /* primary rays re-traced in FP64 */
     uint64_t launches;       /* kernels launched by this library since ptb_counters_reset */
-    uint64_t nodes_visited;  /* instrumented builds only */
-    uint64_t tris_tested;
+    uint64_t nodes_visited;  /* PTB_FLAG_COUNT_NODES runs only: LBVH nodes fetched by closest-hit rays */
+    uint64_t tris_tested;    /* ... triangles tested by closest-hit rays */
+    uint64_t nodes_visited_shadow;
+    uint64_t tris_tested_shadow;
 } ptb_counters;
 
 const char *ptb_last_error(void);

@@ -11,6 +11,7 @@
 #include "ptb_planes.cuh"
 #include "ptb_bvh_build.cuh"
 #include "ptb_bvh_kernels.cuh"
+#include "ptb_bvh_dyn.cuh"
 
 namespace ptb {
 
@@ -90,6 +91,7 @@ struct ptb_scene {
     PlaneScene planes;              // plane-grouped records (brute-force scenes)
     float pad;                      // LBVH box inflation
     bool use_planes;
+    bool bvh_dynamic;               // persistent kernels with dynamic ray fetch (ptb_bvh_dyn.cuh)
 };
 
 template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, const T **out, cudaStream_t st) {
@@ -310,6 +312,9 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     }
     std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
+    std::vector<int> obj_first(no + 2, n);
+    for (int i = n - 1; i >= 0; --i) obj_first[tobj[i]] = i;
+    for (int k = no; k >= 0; --k) if (obj_first[k] == n && k + 1 <= no + 1) obj_first[k] = obj_first[k + 1];
     std::vector<PlaneRec> planes; int n_occ = 0;
     if (accel == PTB_ACCEL_BRUTE) build_plane_groups(desc, tri, planes, n_occ);
 
@@ -318,7 +323,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     if ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
         (rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) || (rc = upload(s, verts, &d.verts64, st)) ||
         (rc = upload(s, normals, &d.normals64, st)) || (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
-        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
+        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, obj_first, &d.obj_first, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
     }
@@ -330,6 +335,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     d.light_total = total;
     s->planes.n_planes = (int)planes.size(); s->planes.n_occ = n_occ;
     s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
+    s->bvh_dynamic = getenv("PTB_BVH_STATIC") == nullptr;
     s->build_ms = 0.0;
     s->n_nodes = 0;
     s->pad = (float)(scale * 3.814697265625e-06);   // 2^-18 * scene scale

@@ -64,6 +64,7 @@ static int check_pixels(const ptb_pixels *px) {
 }
 
 static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
+static unsigned g_work_slot = 0;     // rotates through the 32 work counters of a queue set
 static bool g_count_nodes = false;   // instrumented (untimed) run: count nodes visited / triangles tested
 
 // closest-hit over queue `in` for the brute-force scene
@@ -72,7 +73,16 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
     ProfScope ps_(PK_CLOSEST, st);
     if (s->d.accel == PTB_ACCEL_LBVH) {
         const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
-        if (track)
+        if (s->bvh_dynamic && q.work) {
+            unsigned *work = q.work + (g_work_slot++ & 31);
+            PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
+            if (track)
+                k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+            else if (g_count_nodes)
+                k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+            else
+                k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+        } else if (track)
             k_closest_bvh32<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
         else if (g_count_nodes)
             k_closest_bvh32<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
@@ -224,7 +234,16 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         }
         PTB_LAUNCHED();
         { ProfScope ps_(PK_SHADOW, st);
-        if (d.accel == PTB_ACCEL_LBVH) {
+        if (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic) {
+            unsigned *work = q.work + (g_work_slot++ & 31);
+            PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
+            if (g_count_nodes)
+                k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work);
+            else
+                k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work);
+            PTB_LAUNCHED();
+            k_nee_finish32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
+        } else if (d.accel == PTB_ACCEL_LBVH) {
             if (g_count_nodes)
                 k_shadow_bvh32<true><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
             else
@@ -382,6 +401,7 @@ extern "C" int ptb_counters_read(const ptb_scene *s, ptb_counters *out, void *st
     out->closest_rays = h[CTR_CLOSEST]; out->shadow_rays = h[CTR_SHADOW]; out->shaded = h[CTR_SHADED];
     out->samples = h[CTR_SAMPLES]; out->retraced = h[CTR_RETRACED]; out->launches = g_launches;
     out->nodes_visited = h[CTR_NODES]; out->tris_tested = h[CTR_TRIS];
+    out->nodes_visited_shadow = h[CTR_NODES_SH]; out->tris_tested_shadow = h[CTR_TRIS_SH];
     return PTB_OK;
 }
 

@@ -1,0 +1,268 @@
+// ptb_bvh_dyn.cuh - persistent LBVH traversal kernels with dynamic ray fetch.
+//
+// Secondary and shadow rays are incoherent and their traversal lengths have a heavy tail (a line that
+// runs close to a tessellated wall enters hundreds of leaf boxes; the mean is ~50 nodes).  With one
+// fixed ray per lane a warp runs as long as its longest ray: ncu showed 3.8 of 32 lanes active
+// (profiles/r01c).  Here every warp is persistent: a lane that finishes its ray leaves the inner loop,
+// and as soon as fewer than PTB_DYN_MIN lanes are still traversing the warp breaks out and the idle lanes
+// claim the next rays from a global counter (one atomic per refill).  Results are written per ray when
+// it terminates, so the processing order does not matter.
+//
+// Shadow rays are scheduled per (path, light sample) item - 3 independent items per shaded path - and
+// only record the outcome (occluding object or -1); k_nee_finish32 then completes compute_color
+// (main.py:142-145) per path.  For light sample 2 the query is "lowest OBJECT index among occluders"
+// (the leaked loop variable, main.py:42, 70): once an occluder of object k is known, only subtrees that
+// still contain a triangle of an earlier object (min reference index < first triangle of k) are entered.
+#pragma once
+#include "ptb_bvh_kernels.cuh"
+
+namespace ptb {
+
+#define PTB_DYN_MIN 20     // refill when fewer lanes than this are still traversing
+
+// warp-wide claim of new work items for the lanes with want == true; returns the claimed index or
+// 0xffffffff when the pool [0, count) is exhausted.
+__device__ __forceinline__ unsigned claim_work(bool want, unsigned *work, unsigned count) {
+    const unsigned need = __ballot_sync(0xffffffffu, want);
+    if (!need) return 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31;
+    const int leader = __ffs(need) - 1;
+    unsigned base = 0;
+    if ((int)lane == leader) base = atomicAdd(work, (unsigned)__popc(need));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    const unsigned idx = base + __popc(need & ((1u << lane) - 1u));
+    return (want && idx < count) ? idx : 0xffffffffu;
+}
+
+// ---------------------------------------------------------------- closest hit
+template <bool TRACK, bool COUNT>
+__global__ void __launch_bounds__(PTB_BVH_THREADS)
+k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__restrict__ qd, const unsigned *__restrict__ d_count,
+                    float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
+                    unsigned *work) {
+    const unsigned count = *d_count;
+    unsigned nn = 0, nt = 0;
+    int stack[PTB_BVH_STACK];
+    int sp = 0, node = 0, best_ref = 0x7fffffff;
+    unsigned ray = 0xffffffffu;
+    bool exhausted = false;                 // warp-uniform: the pool ran dry
+    Hit32 h; h.t = 0.f; h.abs_t = 0.f; h.slot = -1;
+    Unc32 uc; uc.init();
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(1.f, 0.f, 0.f);
+    LineBox<float> lb; lb.set(0.f, 0.f, 0.f, 1.f, 1.f, 1.f);
+    while (true) {
+        if (!exhausted) {
+            const bool want = ray == 0xffffffffu;
+            const unsigned idx = claim_work(want, work, count);
+            if (want && idx != 0xffffffffu) {
+                ray = idx;
+                const float4 a = qo[idx], b = qd[idx];
+                o = mk3(a.x, a.y, a.z); d = mk3(b.x, b.y, b.z);
+                lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
+                h.t = 0.f; h.abs_t = 3.0e38f; h.slot = -1; best_ref = 0x7fffffff;
+                uc.init();
+                sp = 0; node = 0;
+            }
+            exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
+        }
+        if (!__any_sync(0xffffffffu, ray != 0xffffffffu)) break;
+        while (ray != 0xffffffffu) {
+            const NodeBoxes n = ld_node(sc.nodes, node);
+            if (COUNT) nn++;
+            float tn0, tf0, tn1, tf1;
+            slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
+            slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
+            const float lim = TRACK ? h.abs_t + uc.best_dt : h.abs_t;
+            const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
+            bool go0 = (tn0 <= tf0) && (k0 <= lim), go1 = (tn1 <= tf1) && (k1 <= lim);
+            const int c0 = n.d.x, c1 = n.d.y;
+#pragma unroll
+            for (int side = 0; side < 2; ++side) {
+                const bool go = side ? go1 : go0;
+                const int c = side ? c1 : c0;
+                if (go && c < 0) {
+                    const int slot = ~c;
+                    const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
+                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                    const float eps = TRACK ? __ldg(reinterpret_cast<const float *>(tp + 3)) : 0.f;
+                    if (COUNT) nt++;
+                    float t, dt = 0.f; bool edge = false;
+                    const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
+                    const int ref = side ? n.d.w : n.d.z;      // leaf: the min-ref field is the triangle itself
+                    const float a = fabsf(t);
+                    const bool ok = hit && (t * t > PTB_ZERO_F);
+                    if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
+                        if (TRACK) {
+                            if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
+                            uc.best_dt = dt; uc.best_edge = edge;
+                        }
+                        h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref;
+                    } else if (TRACK && (hit || edge)) {
+                        uc.comp_lo = fminf(uc.comp_lo, a - dt);
+                    }
+                }
+            }
+            go0 = go0 && c0 >= 0; go1 = go1 && c1 >= 0;
+            if (go0 && go1) {
+                const bool first1 = k1 < k0;
+                stack[sp++] = first1 ? c0 : c1;
+                node = first1 ? c1 : c0;
+            } else if (go0 || go1) {
+                node = go0 ? c0 : c1;
+            } else if (sp > 0) {
+                node = stack[--sp];
+            } else {                                            // ray finished
+                hit_t[ray] = h.t;
+                hit_tri[ray] = h.slot >= 0 ? best_ref : -1;
+                if (TRACK && closest_uncertain32<TRACK>(h, uc)) unc_list[atomicAdd(unc_count, 1u)] = (int)ray;
+                ray = 0xffffffffu;
+            }
+            if (!exhausted && __popc(__activemask()) < PTB_DYN_MIN) break;
+        }
+    }
+    if (COUNT) {
+        for (int s = 16; s > 0; s >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, s); nt += __shfl_xor_sync(0xffffffffu, nt, s); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(sc.counters + CTR_NODES, (unsigned long long)nn); atomicAdd(sc.counters + CTR_TRIS, (unsigned long long)nt); }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sc.counters + CTR_CLOSEST, (unsigned long long)count);
+}
+
+// ---------------------------------------------------------------- shadow rays: one item per (path, light sample)
+// sh_res[s * cap + j] = occluding object index (lowest one for s == 2), or -1
+template <bool COUNT>
+__global__ void __launch_bounds__(PTB_BVH_THREADS)
+k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const unsigned *__restrict__ d_count,
+                   int *__restrict__ sh_res, int cap, unsigned *work) {
+    const unsigned paths = *d_count;
+    const unsigned count = 3u * paths;
+    unsigned nn = 0, nt = 0;
+    int stack[PTB_BVH_STACK];
+    int sp = 0, node = 0, found = 0x7fffffff, found_obj = -1;
+    unsigned item = 0xffffffffu, out_slot = 0;
+    bool exhausted = false, want_min = false;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(1.f, 0.f, 0.f);
+    float d2max = 0.f, lim = 0.f;
+    LineBox<float> lb; lb.set(0.f, 0.f, 0.f, 1.f, 1.f, 1.f);
+    while (true) {
+        if (!exhausted) {
+            const bool want = item == 0xffffffffu;
+            const unsigned idx = claim_work(want, work, count);
+            if (want && idx != 0xffffffffu) {
+                item = idx;
+                const unsigned s = idx / paths, j = idx - s * paths;     // sample-major: neighbouring lanes, neighbouring paths
+                out_slot = s * (unsigned)cap + j;
+                const float4 pk = sh_p[j], dv = sh_d[out_slot];
+                o = mk3(pk.x, pk.y, pk.z); d = mk3(dv.x, dv.y, dv.z);
+                d2max = dv.w; lim = sqrtf(dv.w) * 1.000001f;
+                lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
+                want_min = s == 2u;
+                found = 0x7fffffff; found_obj = -1;
+                sp = 0; node = 0;
+            }
+            exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
+        }
+        if (!__any_sync(0xffffffffu, item != 0xffffffffu)) break;
+        while (item != 0xffffffffu) {
+            const NodeBoxes n = ld_node(sc.nodes, node);
+            if (COUNT) nn++;
+            float tn0, tf0, tn1, tf1;
+            slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
+            slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
+            const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
+            // subtrees matter only while they can still hold a triangle of an earlier object
+            const int cut = min(found, sc.n_tri_obj);
+            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut);
+            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut);
+            const int c0 = n.d.x, c1 = n.d.y;
+            bool finished = false;
+#pragma unroll
+            for (int side = 0; side < 2; ++side) {
+                const bool go = side ? go1 : go0;
+                const int c = side ? c1 : c0;
+                if (go && c < 0) {
+                    const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + ~c);
+                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                    if (COUNT) nt++;
+                    float t, dt; bool edge;
+                    const bool hit = tri_test32<false>(q0, q1, q2, 0.f, o, d, 0.f, t, edge, dt);
+                    const float t2 = t * t;
+                    if (hit && t2 >= PTB_ZERO_F && t2 < d2max) {
+                        const int ref = side ? n.d.w : n.d.z;
+                        if (ref < found) {
+                            found_obj = __ldg(sc.tri_obj + ref);
+                            found = __ldg(sc.obj_first + found_obj);    // first triangle of that object
+                        }
+                        if (!want_min || found == 0) finished = true;
+                    }
+                }
+            }
+            go0 = go0 && c0 >= 0 && (n.d.z < found); go1 = go1 && c1 >= 0 && (n.d.w < found);
+            if (!finished) {
+                if (go0 && go1) {
+                    const bool first1 = k1 < k0;
+                    stack[sp++] = first1 ? c0 : c1;
+                    node = first1 ? c1 : c0;
+                } else if (go0 || go1) node = go0 ? c0 : c1;
+                else if (sp > 0) node = stack[--sp];
+                else finished = true;
+            }
+            if (finished) {
+                sh_res[out_slot] = found_obj;
+                item = 0xffffffffu;
+            }
+            if (!exhausted && __popc(__activemask()) < PTB_DYN_MIN) break;
+        }
+    }
+    if (COUNT) {
+        for (int s = 16; s > 0; s >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, s); nt += __shfl_xor_sync(0xffffffffu, nt, s); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(sc.counters + CTR_NODES_SH, (unsigned long long)nn); atomicAdd(sc.counters + CTR_TRIS_SH, (unsigned long long)nt); }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(sc.counters + CTR_SHADOW, (unsigned long long)count);
+        atomicAdd(sc.counters + CTR_SHADED, (unsigned long long)paths);
+    }
+}
+
+// ---------------------------------------------------------------- NEE finish (main.py:61-73, 142-145, 230-231)
+__global__ void __launch_bounds__(256)
+k_nee_finish32(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const int2 *__restrict__ sh_aux,
+               const int *__restrict__ sh_res, const unsigned *__restrict__ d_count, float4 *__restrict__ L, int cap, int bounce,
+               RecPtrs rec) {
+    const unsigned count = *d_count;
+    const float lc0 = (float)sc.light_color[0], lc1 = (float)sc.light_color[1], lc2 = (float)sc.light_color[2];
+    const float ambient = (float)sc.ambient;
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
+        const float4 pk = sh_p[j];
+        const int2 aux = sh_aux[j];
+        const float4 sn = __ldg(sc.tri_sn + aux.y);
+        const int obj = __float_as_int(sn.w);
+        float dot_sum = 0.f;
+        int occ = 0, leak = sc.n_obj - 1;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+            const int r = sh_res[(size_t)s * cap + j];
+            if (r >= 0) { occ |= 1 << s; if (s == 2) leak = r; }
+            else {
+                const float4 dv = sh_d[(size_t)s * cap + j];
+                dot_sum += fmaf(dv.z, sn.z, fmaf(dv.y, sn.y, dv.x * sn.x));
+            }
+        }
+        const float dotv = dot_sum / 3.0f;
+        const float *m = sc.mat32 + 8 * obj, *lm = sc.mat32 + 8 * leak;
+        const float ka = __ldg(m + 3);
+        const float c0 = __ldg(m + 0) * ka * ambient + lc0 * __ldg(lm + 0) * dotv;
+        const float c1 = __ldg(m + 1) * ka * ambient + lc1 * __ldg(lm + 1) * dotv;
+        const float c2 = __ldg(m + 2) * ka * ambient + lc2 * __ldg(lm + 2) * dotv;
+        float4 l = L[aux.x];
+        l.x = fmaf(c0, pk.w, l.x); l.y = fmaf(c1, pk.w, l.y); l.z = fmaf(c2, pk.w, l.z);
+        L[aux.x] = l;
+        if (rec.any) {
+            const size_t ri = rec.index(aux.x, bounce);
+            if (rec.occ) rec.occ[ri] = (int8_t)occ;
+            if (rec.leak) rec.leak[ri] = (int8_t)leak;
+            if (rec.contrib) { rec.contrib[3 * ri] = c0 * pk.w; rec.contrib[3 * ri + 1] = c1 * pk.w; rec.contrib[3 * ri + 2] = c2 * pk.w; }
+        }
+    }
+}
+
+}  // namespace ptb

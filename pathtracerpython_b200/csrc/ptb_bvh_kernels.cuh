@@ -54,7 +54,7 @@ k_shadow_bvh32(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restr
     }
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); nt += __shfl_xor_sync(0xffffffffu, nt, o); }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(sc.counters + CTR_NODES, (unsigned long long)nn); atomicAdd(sc.counters + CTR_TRIS, (unsigned long long)nt); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(sc.counters + CTR_NODES_SH, (unsigned long long)nn); atomicAdd(sc.counters + CTR_TRIS_SH, (unsigned long long)nt); }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(sc.counters + CTR_SHADOW, 3ull * count);

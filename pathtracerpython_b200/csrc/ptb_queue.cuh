@@ -37,6 +37,8 @@ template <typename T> struct Queues {
     int *hit_tri;
     v4 *sh_p, *sh_d;       // sh_d is [3][cap]
     int2 *sh_aux;
+    int *sh_res;           // [3][cap] LBVH shadow outcome per (light sample, path): occluding object or -1
+    unsigned *work;        // dynamic-fetch counters of the persistent LBVH kernels
     v4 *L;
     unsigned *count;       // [bounces + 2] live-path count entering each bounce
     unsigned *unc_count;   // number of uncertain primary rays
@@ -46,8 +48,8 @@ template <typename T> struct Queues {
 
 template <typename T> inline size_t queue_bytes(size_t cap, int bounces) {
     size_t v = sizeof(typename VecT<T>::v4);
-    size_t per = 4 * v + sizeof(T) + sizeof(int) + v + 3 * v + sizeof(int2) + v + sizeof(int);
-    return per * cap + 256 * 16 + (size_t)(bounces + 8) * sizeof(unsigned);
+    size_t per = 4 * v + sizeof(T) + sizeof(int) + v + 3 * v + sizeof(int2) + v + sizeof(int) + 3 * sizeof(int);
+    return per * cap + 256 * 20 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
 }
 
 // carve a workspace into queues; returns bytes used (0 if it does not fit)
@@ -65,6 +67,8 @@ template <typename T> inline size_t queue_carve(void *ws, size_t bytes, size_t c
     q.hit_tri = (int *)take(cap * sizeof(int));
     q.sh_aux = (int2 *)take(cap * sizeof(int2));
     q.unc_list = (int *)take(cap * sizeof(int));
+    q.sh_res = (int *)take(3 * cap * sizeof(int));
+    q.work = (unsigned *)take(256);
     q.count = (unsigned *)take((size_t)(bounces + 4) * sizeof(unsigned));
     q.unc_count = (unsigned *)take(4 * sizeof(unsigned));
     q.cap = (int)cap;

@@ -34,6 +34,7 @@ struct DScene {
     const double *mat64;      // [n_obj+1][8]
     const double *light_cdf;  // [n_light_tri+1] running sums of light_obj.areas (utils.py:31-35)
     const int *tri_obj;       // [n_tri]
+    const int *obj_first;     // [n_obj+2] first reference triangle of every object (light = n_obj), then n_tri
     // --- acceleration structure (accel == PTB_ACCEL_LBVH)
     const BvhNode *nodes;     // [n_tri-1]; root = 0
     const BvhNode *nodes_occ; // BVH over the occlusion set (object triangles only)
@@ -48,6 +49,6 @@ struct DScene {
 
 // offsets into DScene::counters (u64 units)
 enum { CTR_CLOSEST = 0, CTR_SHADOW = 1, CTR_SHADED = 2, CTR_SAMPLES = 3, CTR_RETRACED = 4, CTR_LAUNCHES = 5,
-       CTR_NODES = 6, CTR_TRIS = 7, CTR_COUNT = 8 };
+       CTR_NODES = 6, CTR_TRIS = 7, CTR_NODES_SH = 8, CTR_TRIS_SH = 9, CTR_COUNT = 10 };
 
 }  // namespace ptb

@@ -186,6 +186,12 @@ class Renderer:
                        "ptb_scatter_accum")
         return accum_full
 
+    def info(self):
+        """-> dict(accel, n_nodes, build_ms) of the device scene."""
+        a, n, ms = C.c_int32(), C.c_int32(), C.c_double()
+        _lib.check(_lib.lib().ptb_scene_info(self._handle, C.byref(a), C.byref(n), C.byref(ms)), "ptb_scene_info")
+        return {"accel": {1: "brute", 2: "lbvh"}.get(a.value, a.value), "n_nodes": n.value, "build_ms": ms.value}
+
     def counters(self, reset=False):
         c = _lib.Counters()
         with self.torch.cuda.device(self.device):

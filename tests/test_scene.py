@@ -78,7 +78,7 @@ def test_struct_layouts_match_header():
     assert ctypes.sizeof(_lib.Pixels) == 32
     assert ctypes.sizeof(_lib.RenderParams) == 64
     assert ctypes.sizeof(_lib.PathRecords) == 64
-    assert ctypes.sizeof(_lib.Counters) == 64
+    assert ctypes.sizeof(_lib.Counters) == 80
 
 
 def test_pixel_sharding_partition():
