@@ -21,6 +21,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 
 F_TEST = 38          # FP32 flops of one ray-triangle test as written in ptb_isect.cuh (FMA = 2); DESIGN.md
 RAY_STATE_BYTES = {"closest_hit": 32 + 8, "shadow": 16 + 48 + 8 + 32, "shade": 40 + 32 + 72}
@@ -38,6 +40,7 @@ def parse():
     ap.add_argument("--scene", default=None)
     ap.add_argument("--tess", type=int, default=0, help="tessellate every triangle into N x N (configs 4/5: 177 -> 1.0M, 559 -> 10.0M triangles)")
     ap.add_argument("--seed", type=int, default=9)
+    ap.add_argument("--shard", default="tile", choices=["tile", "sample"], help="multi-GPU partition (SURVEY.md 8e)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the bounded baseline sample")
     return ap.parse_args()
@@ -140,7 +143,7 @@ def run_ours(a):
     import torch
     import torch.distributed as dist
     import pathtracerpython_b200 as ptb
-    from pathtracerpython_b200 import _lib
+    from pathtracerpython_b200 import _lib, dist as pdist
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -161,15 +164,8 @@ def run_ours(a):
     host_img = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory()
 
     def step(rnd):
-        acc, _ = rnd.trace_paths(a.spp, a.bounces, seed=a.seed, width=W, height=H, shard=rank, n_shards=world, tile=H)
-        if world > 1:
-            full.zero_()
-            rnd.scatter(px, acc, full)
-            dist.reduce(full, dst=0)
-            frame = full
-        else:
-            frame = acc
-        return rnd.image(frame, W, H) if rank == 0 else None
+        img, _ = pdist.render_step(rnd, a.spp, a.bounces, a.seed, W, H, rank, world, a.shard, H, full)
+        return img
 
     def timed(fn, steps):
         if world > 1:
@@ -241,7 +237,8 @@ def run_ours(a):
     if info["accel"] == "lbvh":
         # instrumented, untimed pass of the same kernels on the same LBVH: nodes fetched / triangles tested per ray
         r.counters(reset=True)
-        r.trace_paths(1, a.bounces, seed=a.seed, width=W, height=H, shard=rank, n_shards=world, tile=H, flags=_lib.FLAG_COUNT_NODES)
+        r.trace_paths(1, a.bounces, seed=a.seed, width=W, height=H, shard=rank if a.shard == "tile" else 0,
+                      n_shards=world if a.shard == "tile" else 1, tile=H, flags=_lib.FLAG_COUNT_NODES)
         ci = r.counters(reset=True)
         n_ch, t_ch = ci["nodes_visited"] / max(1, ci["closest_rays"]), ci["tris_tested"] / max(1, ci["closest_rays"])
         n_sh, t_sh = ci["nodes_visited_shadow"] / max(1, ci["shadow_rays"]), ci["tris_tested_shadow"] / max(1, ci["shadow_rays"])
@@ -288,7 +285,7 @@ def run_ours(a):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "scene": os.path.basename(scene_path), "triangles": n_tri,
                    "accel": info["accel"], "bvh_build_ms": info["build_ms"],
-                   "width": W, "height": H, "spp": a.spp, "bounces": a.bounces, "sharding": f"column-interleaved tiles x{world}",
+                   "width": W, "height": H, "spp": a.spp, "bounces": a.bounces, "sharding": (f"column-interleaved tiles x{world}" if a.shard == "tile" else f"sample ranges x{world}"),
                    "l2_policy": "inputs larger than L2 (wavefront state of one batch is GBs)"},
         "mrays_per_s": float(rays[0]) / sec / 1e6, "closest_mrays_per_s": float(rays[1]) / sec / 1e6,
         "shadow_mrays_per_s": float(rays[2]) / sec / 1e6, "rays_per_sample": float(rays[0]) / samples,
