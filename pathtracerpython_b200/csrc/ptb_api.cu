@@ -176,7 +176,23 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
         pr.a1 = tri[ta].q1; pr.a2 = tri[ta].q2;
         if (tb >= 0) { pr.b1 = tri[tb].q1; pr.b2 = tri[tb].q2; }
         else { pr.b1 = make_float4(0.f, 0.f, 0.f, -1.f); pr.b2 = make_float4(0.f, 0.f, 0.f, -1.f); }
-        pr.ref_a = ta; pr.ref_b = tb; pr.min_ref = ta;
+        pr.ref_a = ta; pr.ref_b = tb; pr.kind = 0;
+        if (tb >= 0) {   // parallelogram: B's vertex set == {a1, a3, a1 + a3 - a2}
+            const double *A = desc->verts + 9 * (size_t)ta, *B = desc->verts + 9 * (size_t)tb;
+            double want[3][3];
+            for (int k = 0; k < 3; ++k) { want[0][k] = A[k]; want[1][k] = A[6 + k]; want[2][k] = A[k] + A[6 + k] - A[3 + k]; }
+            bool used[3] = {false, false, false};
+            int matched = 0;
+            for (int w = 0; w < 3; ++w)
+                for (int v = 0; v < 3; ++v) {
+                    if (used[v]) continue;
+                    const double tol = (w < 2 ? 0.0 : 1e-12 * scale);
+                    if (fabs(B[3 * v] - want[w][0]) <= tol && fabs(B[3 * v + 1] - want[w][1]) <= tol && fabs(B[3 * v + 2] - want[w][2]) <= tol) {
+                        used[v] = true; ++matched; break;
+                    }
+                }
+            if (matched == 3) pr.kind = 1;
+        }
         pr.n_obj = ta < desc->n_tri_obj ? (tb >= 0 ? 2 : 1) : 0;
         if (pr.n_obj) n_occ++;
         planes.push_back(pr);
@@ -310,6 +326,26 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         acc = acc + desc->light_areas[i];
         cdf[i + 1] = acc;
     }
+    // Integer thresholds on the 24-bit uniform m = x >> 8 (u = m * 2^-24) that reproduce the reference's FP64
+    // comparisons exactly: both products below are monotone in m, so a bisection finds the switch point.
+    auto first_m = [](auto pred) {            // smallest m in [0, 2^24] with pred(m) true (pred monotone), 2^24 if none
+        unsigned lo = 0, hi = 1u << 24;
+        if (pred(0u)) return 0u;
+        while (hi - lo > 1) { unsigned mid = (lo + hi) >> 1; if (pred(mid)) hi = mid; else lo = mid; }
+        return pred(hi) ? hi : (1u << 24);
+    };
+    std::vector<unsigned> light_thr(desc->n_light_tri);
+    for (int i = 0; i < desc->n_light_tri; ++i) {
+        const double c = cdf[i];              // pick_random_triangle: cum[i] <= uniform(0, total)  (utils.py:30, 38)
+        light_thr[i] = i == 0 ? 0u : first_m([&](unsigned m) { return 0.0 + (total - 0.0) * ((double)m * 5.9604644775390625e-08) >= c; });
+    }
+    std::vector<int> lobe_thr(no + 1, 0), pow_int(no + 1, -1);
+    for (int k = 0; k < no; ++k) {
+        const double kd = desc->mat[8 * k + 4], ks = desc->mat[8 * k + 5], ne = desc->mat[8 * k + 7];
+        // diffuse iff uniform(0, kd + ks) <= kd  (main.py:240-241)  <=>  m < first m with the product > kd
+        lobe_thr[k] = (int)first_m([&](unsigned m) { return !(0.0 + ((kd + ks) - 0.0) * ((double)m * 5.9604644775390625e-08) <= kd); });
+        if (ne >= 0.0 && ne <= 64.0 && ne == floor(ne)) pow_int[k] = (int)ne;
+    }
     std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<int> obj_first(no + 2, n);
@@ -323,7 +359,8 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     if ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
         (rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) || (rc = upload(s, verts, &d.verts64, st)) ||
         (rc = upload(s, normals, &d.normals64, st)) || (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
-        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, obj_first, &d.obj_first, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
+        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, obj_first, &d.obj_first, st)) ||
+        (rc = upload(s, light_thr, &d.light_thr, st)) || (rc = upload(s, lobe_thr, &d.obj_lobe_thr, st)) || (rc = upload(s, pow_int, &d.obj_pow_int, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
     }

@@ -88,6 +88,20 @@ __device__ __forceinline__ uint4 rng4(uint32_t seed, uint32_t pixel, uint32_t sa
 }
 template <typename T> __device__ __forceinline__ T u01(uint32_t w) { return (T)(w >> 8) * (T)5.9604644775390625e-08; }
 
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// id / d and id % d for a warp-uniform divisor without the integer-division sequence: float estimate
+// + one correction step (exact for id < 2^31 whenever id / d < 2^23, which the batch limits guarantee)
+__device__ __forceinline__ void fast_divmod(int id, int d, float inv_d, int &q, int &r) {
+    q = (int)((float)id * inv_d);
+    r = id - q * d;
+    if (r < 0) { r += d; --q; }
+    else if (r >= d) { r -= d; ++q; }
+}
+
 // ---------------------------------------------------------------- pixel-set mapping (ptb_pixels)
 struct PixelMap {
     int W, H, shard, n_shards, tile, n;

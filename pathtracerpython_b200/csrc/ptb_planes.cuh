@@ -18,7 +18,7 @@ struct PlaneRec {      // 96 B = 6 x float4: one supporting plane + up to two of
     float4 b1, b2;     // triangle B (or a never-inside dummy: u == -1)
     int ref_a, ref_b;  // reference triangle indices (ref_b = -1 for the dummy)
     int n_obj;         // how many of (A, B) belong to the occlusion set: 0, 1 (A only) or 2
-    int min_ref;       // == ref_a
+    int kind;          // 1: A = (a1,a2,a3), B = (a1,a3,a1+a3-a2) form a parallelogram -> one test for both
 };
 struct PlaneScene {    // device pointer, small; staged into shared memory by every block
     const PlaneRec *planes;   // groups with n_obj > 0 first (n_occ of them), light-only groups last
@@ -34,15 +34,20 @@ __device__ __forceinline__ const PlaneRec *stage_planes(unsigned char *smem, con
     return reinterpret_cast<const PlaneRec *>(smem);
 }
 
+// Parallelogram pair: with (u, v) the barycentrics of triangle A, P = a1 + (u+v)(a2-a1) + v(a4-a1), so P is in
+// the quad iff 0 < v < 1 and 0 < u+v < 1; u > 0 selects A, u < 0 selects B, u == 0 is the shared diagonal
+// (an edge of both triangles: miss, A-Q15).  6 FMA + 4 ALU instead of 2 x (6 FMA + 4 ALU).
+__device__ __forceinline__ bool para_hit(const float4 q1, const float4 q2, float px, float py, float pz, float &u) {
+    u = fmaf(q1.z, pz, fmaf(q1.y, py, fmaf(q1.x, px, q1.w)));
+    const float v = fmaf(q2.z, pz, fmaf(q2.y, py, fmaf(q2.x, px, q2.w)));
+    const float vh = v - 0.5f, sh = u + vh;
+    return (fmaxf(fabsf(vh), fabsf(sh)) < 0.5f) && (u != 0.0f);
+}
+
 __device__ __forceinline__ float bary_min(const float4 q1, const float4 q2, float px, float py, float pz) {
     const float u = fmaf(q1.z, pz, fmaf(q1.y, py, fmaf(q1.x, px, q1.w)));
     const float v = fmaf(q2.z, pz, fmaf(q2.y, py, fmaf(q2.x, px, q2.w)));
     return fminf(fminf(u, v), 1.0f - u - v);
-}
-__device__ __forceinline__ float rcp_approx(float x) {
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
 }
 
 #define PTB_TMIN_F 3.1622776e-3f   // sqrt(1e-5): |t| threshold equivalent to squared_dist > ZERO
@@ -71,11 +76,18 @@ k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, cons
             const bool ok = (fabsf(dn) > PTB_ZERO_F) && (at > PTB_TMIN_F) && (at < best_a);
             if (!__any_sync(0xffffffffu, ok)) continue;
             const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
-            const float ma = bary_min(planes[g].a1, planes[g].a2, px, py, pz);
-            const float mb = bary_min(planes[g].b1, planes[g].b2, px, py, pz);
-            // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
-            const bool ha = ok && ma > 0.0f, hb = ok && mb > 0.0f;
-            if (ha || hb) { best_a = at; best_t = t; best_ref = ha ? planes[g].ref_a : planes[g].ref_b; }
+            if (planes[g].kind) {                   // warp-uniform
+                float u;
+                if (para_hit(planes[g].a1, planes[g].a2, px, py, pz, u) && ok) {
+                    best_a = at; best_t = t; best_ref = u > 0.0f ? planes[g].ref_a : planes[g].ref_b;
+                }
+            } else {
+                const float ma = bary_min(planes[g].a1, planes[g].a2, px, py, pz);
+                const float mb = bary_min(planes[g].b1, planes[g].b2, px, py, pz);
+                // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
+                const bool ha = ok && ma > 0.0f, hb = ok && mb > 0.0f;
+                if (ha || hb) { best_a = at; best_t = t; best_ref = ha ? planes[g].ref_a : planes[g].ref_b; }
+            }
         }
         if (live) {
             hit_t[i] = best_t;
@@ -115,25 +127,35 @@ k_shadow_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ sh_p, con
             // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
             const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w);
             const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w);
-            const bool ok2 = (planes[g].min_ref < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
+            const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
             if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
             const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
             const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);
             const float p2x = fmaf(t2, d2.x, pk.x), p2y = fmaf(t2, d2.y, pk.y), p2z = fmaf(t2, d2.z, pk.z);
             const float4 a1 = planes[g].a1, a2 = planes[g].a2;
-            const bool ha0 = bary_min(a1, a2, p0x, p0y, p0z) > 0.0f;
-            const bool ha1 = bary_min(a1, a2, p1x, p1y, p1z) > 0.0f;
-            const bool ha2 = bary_min(a1, a2, p2x, p2y, p2z) > 0.0f;
-            bool hb0 = false, hb1 = false, hb2 = false;
-            if (planes[g].n_obj > 1) {             // warp-uniform
-                const float4 b1 = planes[g].b1, b2 = planes[g].b2;
-                hb0 = bary_min(b1, b2, p0x, p0y, p0z) > 0.0f;
-                hb1 = bary_min(b1, b2, p1x, p1y, p1z) > 0.0f;
-                hb2 = bary_min(b1, b2, p2x, p2y, p2z) > 0.0f;
+            if (planes[g].kind) {                  // warp-uniform: parallelogram pair, both triangles in the occlusion set
+                float u0, u1, u2;
+                const bool h0 = para_hit(a1, a2, p0x, p0y, p0z, u0);
+                const bool h1 = para_hit(a1, a2, p1x, p1y, p1z, u1);
+                const bool h2 = para_hit(a1, a2, p2x, p2y, p2z, u2);
+                occ0 = occ0 || (ok0 && h0);
+                occ1 = occ1 || (ok1 && h1);
+                if (ok2 && h2) leak_ref = min(leak_ref, u2 > 0.0f ? planes[g].ref_a : planes[g].ref_b);
+            } else {
+                const bool ha0 = bary_min(a1, a2, p0x, p0y, p0z) > 0.0f;
+                const bool ha1 = bary_min(a1, a2, p1x, p1y, p1z) > 0.0f;
+                const bool ha2 = bary_min(a1, a2, p2x, p2y, p2z) > 0.0f;
+                bool hb0 = false, hb1 = false, hb2 = false;
+                if (planes[g].n_obj > 1) {             // warp-uniform
+                    const float4 b1 = planes[g].b1, b2 = planes[g].b2;
+                    hb0 = bary_min(b1, b2, p0x, p0y, p0z) > 0.0f;
+                    hb1 = bary_min(b1, b2, p1x, p1y, p1z) > 0.0f;
+                    hb2 = bary_min(b1, b2, p2x, p2y, p2z) > 0.0f;
+                }
+                occ0 = occ0 || (ok0 && (ha0 || hb0));
+                occ1 = occ1 || (ok1 && (ha1 || hb1));
+                if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
             }
-            occ0 = occ0 || (ok0 && (ha0 || hb0));
-            occ1 = occ1 || (ok1 && (ha1 || hb1));
-            if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
         }
         if (!live) continue;
         const int2 aux = sh_aux[j];

@@ -81,6 +81,24 @@ __device__ __forceinline__ int pick_light(const double *cdf, int n, double x) {
     return lo;
 }
 
+// integer form of the same pick: thr[i] = smallest 24-bit m whose product total * m * 2^-24 reaches
+// cum[i] (built on the host in FP64), so the choice is bit-identical and needs no FP64 on the device
+__device__ __forceinline__ int pick_light_int(const unsigned *thr, int n, unsigned m) {
+    if (n == 2) return m >= __ldg(thr + 1) ? 1 : 0;
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(thr + mid) <= m) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+// x^n for a small non-negative integer n (negative bases keep their sign like pow with an integral exponent)
+__device__ __forceinline__ float pow_small_int(float x, int n) {
+    float r = 1.0f;
+    while (n) { if (n & 1) r *= x; x *= x; n >>= 1; }
+    return r;
+}
+
 __global__ void __launch_bounds__(PTB_SHADE_THREADS)
 k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
           const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
@@ -89,6 +107,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
           int cap, RecPtrs rec) {
     const unsigned count = *d_count_in;
     const float ex = (float)sc.eye[0], ey = (float)sc.eye[1], ez = (float)sc.eye[2];
+    const float inv_npix = 1.0f / (float)bi.npix;
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
         const unsigned i = base + threadIdx.x;
         bool alive = false;
@@ -122,16 +141,17 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         const f3 o = mk3(a.x, a.y, a.z), d = mk3(b.x, b.y, b.z), n = mk3(sn.x, sn.y, sn.z);
         const float k = a.w;
         const f3 P = mk3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
-        const int s_local = id / bi.npix, p = id - s_local * bi.npix;
+        int s_local, p;
+        fast_divmod(id, bi.npix, inv_npix, s_local, p);
         const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
 
         // ---- 3 light samples (main.py:30-40)
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
             const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);
-            const int li = pick_light(sc.light_cdf, sc.n_light_tri, sc.light_total * u01<double>(w.x));
+            const int li = pick_light_int(sc.light_thr, sc.n_light_tri, w.x >> 8);
             const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
-            const float inv = 1.0f / ((c0 + c1) + c2);
+            const float inv = rcp_approx((c0 + c1) + c2);
             const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
             const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
             const f3 v = mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)) - P.x,
@@ -146,8 +166,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
 
         // ---- bounce (main.py:240-264)
         const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, 3u);
-        const double kd = __ldg(sc.mat64 + 8 * obj + 4), ks = __ldg(sc.mat64 + 8 * obj + 5);
-        const bool diffuse = ((kd + ks) * u01<double>(w.x)) <= kd;
+        const bool diffuse = (int)(w.x >> 8) < __ldg(sc.obj_lobe_thr + obj);
         const float cy = n.y, sy = sqrtf(fmaxf(0.f, fmaf(-cy, cy, 1.0f)));   // cos / sin of arccos(n.y)
         f3 v; float knew;
         if (diffuse) {
@@ -164,11 +183,14 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         }
         const f3 wv = mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));   // R_y(arccos(n.y)) (main.py:148-162)
         if (diffuse) {
-            knew = k * ((float)kd * dot(wv, n));
+            knew = k * (__ldg(sc.mat32 + 8 * obj + 4) * dot(wv, n));
         } else {
             f3 e = mk3(ex - P.x, ey - P.y, ez - P.z);
             e = e * rsqrtf(dot(e, e));
-            knew = k * ((float)ks * powf(dot(e, wv), __ldg(sc.mat32 + 8 * obj + 7)));
+            const int pn = __ldg(sc.obj_pow_int + obj);
+            const float ew = dot(e, wv);
+            const float pw = pn >= 0 ? pow_small_int(ew, pn) : powf(ew, __ldg(sc.mat32 + 8 * obj + 7));
+            knew = k * (__ldg(sc.mat32 + 8 * obj + 5) * pw);
         }
         qo_out[j] = make_float4(P.x, P.y, P.z, knew);
         qd_out[j] = make_float4(wv.x, wv.y, wv.z, __int_as_float(id));
