@@ -149,10 +149,10 @@ int ptb_scatter_accum(const ptb_pixels *px, const float *d_accum_shard, float *d
 
 /* Per-kernel-class device timing (CUDA events on the launch stream), for the roofline report.
  * kinds: 0 camera rays, 1 closest-hit, 2 FP64 re-trace, 3 shade/bounce, 4 shadow/any-hit + NEE,
- * 5 batch reduce, 6 tone map, 7 other, 8 LBVH build.  ptb_profile_read synchronises the device,
+ * 5 batch reduce, 6 tone map, 7 other, 8 LBVH build, 9 per-bounce ray sort.  ptb_profile_read synchronises the device,
  * writes the accumulated milliseconds and launch counts per kind (arrays of PTB_PROF_KINDS) and
  * clears the accumulators. */
-#define PTB_PROF_KINDS 9
+#define PTB_PROF_KINDS 10
 int ptb_profile_enable(int on);
 int ptb_profile_read(double *ms_per_kind, uint64_t *launches_per_kind);
 

@@ -48,7 +48,7 @@ class Counters(C.Structure):
                                           "nodes_visited", "tris_tested", "nodes_visited_shadow", "tris_tested_shadow")]
 
 
-PROF_KINDS = ["camera", "closest_hit", "fp64_retrace", "shade", "shadow", "reduce", "tonemap", "other", "bvh_build"]
+PROF_KINDS = ["camera", "closest_hit", "fp64_retrace", "shade", "shadow", "reduce", "tonemap", "other", "bvh_build", "ray_sort"]
 
 _lib = None
 

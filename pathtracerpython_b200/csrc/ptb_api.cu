@@ -43,7 +43,7 @@ static int grid_for(size_t work, int threads, int blocks_per_sm) {
 }
 
 // ---- optional per-kernel-class timing with CUDA events on the launch stream
-enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD };
+enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD, PK_SORT };
 struct ProfRec { int kind; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;
@@ -92,6 +92,7 @@ struct ptb_scene {
     float pad;                      // LBVH box inflation
     bool use_planes;
     bool bvh_dynamic;               // persistent kernels with dynamic ray fetch (ptb_bvh_dyn.cuh)
+    bool sort_rays;                 // per-bounce Morton re-ordering of the live paths (ptb_sort.cuh)
 };
 
 template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, const T **out, cudaStream_t st) {
@@ -201,9 +202,11 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
 
 // GPU LBVH build (ptb_bvh_build.cuh).  Temporary buffers are freed before returning; the handle keeps
 // the 64 B nodes, the leaf-ordered TriRec array and the slot -> reference index table.
-static int build_lbvh(ptb_scene *s, cudaStream_t st) {
+// Builds over the first `n` triangles of the scene (reference order): n = n_tri gives the closest-hit tree,
+// n = n_tri_obj the occlusion tree (main.py:42 loops over scene.objects only; the light mesh is last).
+static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
+                      const int **ids_out, double *ms_out, cudaStream_t st) {
     DScene &d = s->d;
-    const int n = d.n_tri;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
@@ -251,7 +254,7 @@ static int build_lbvh(ptb_scene *s, cudaStream_t st) {
         k_karras<<<g, 256, 0, st>>>(keys[0], n, child, parent_inner, parent_leaf);
         k_refit<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, parent_inner, parent_leaf, node_box, node_minref, flags);
         k_pack<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, node_box, node_minref, s->pad, nodes);
-        k_gather_tris<<<g, 256, 0, st>>>(n, vals[1], d.tri, tri_sorted);
+        k_gather_tris<<<g, 256, 0, st>>>(n, vals[1], src_tri, tri_sorted);
         g_launches += 4;
     }
     cudaEventRecord(e1, st);
@@ -262,11 +265,10 @@ static int build_lbvh(ptb_scene *s, cudaStream_t st) {
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     for (void *p : tmp) cudaFree(p);
     if (err != cudaSuccess) { set_error("LBVH build failed: %s", cudaGetErrorString(err)); return PTB_ERR_CUDA; }
-    d.nodes = nodes;
-    d.tri = tri_sorted;       // leaf order; the reference-order array stays allocated but unused
-    d.tri_id = vals[1];
-    s->build_ms = ms;
-    s->n_nodes = n - 1;
+    *nodes_out = nodes;
+    *tri_out = tri_sorted;    // leaf order
+    *ids_out = vals[1];
+    *ms_out = ms;
     return PTB_OK;
 }
 
@@ -373,10 +375,28 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     s->planes.n_planes = (int)planes.size(); s->planes.n_occ = n_occ;
     s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
     s->bvh_dynamic = getenv("PTB_BVH_STATIC") == nullptr;
+    s->sort_rays = getenv("PTB_NO_SORT") == nullptr;
     s->build_ms = 0.0;
     s->n_nodes = 0;
     s->pad = (float)(scale * 3.814697265625e-06);   // 2^-18 * scene scale
-    if (accel == PTB_ACCEL_LBVH && (rc = build_lbvh(s, st))) { ptb_scene_destroy(s); return rc; }
+    {   // scene box of the per-bounce sort keys (ptb_sort.cuh)
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (size_t i = 0; i < (size_t)n * 3; ++i)
+            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], desc->verts[3 * i + k]); hi[k] = std::max(hi[k], desc->verts[3 * i + k]); }
+        for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)lo[k]; d.bb_inv[k] = (float)(256.0 / std::max(hi[k] - lo[k], 1e-30)); }
+    }
+    if (accel == PTB_ACCEL_LBVH) {
+        const TriRec *ref_order = d.tri;      // the reference-order array stays allocated: source of both gathers
+        double ms_all = 0.0, ms_occ = 0.0;
+        if ((rc = build_lbvh(s, n, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, st))) { ptb_scene_destroy(s); return rc; }
+        if (d.n_tri_obj >= 2) {
+            if ((rc = build_lbvh(s, d.n_tri_obj, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, st))) { ptb_scene_destroy(s); return rc; }
+        } else {                              // degenerate occlusion set: fall back to the full tree + min-ref pruning
+            d.nodes_occ = nullptr; d.tri_occ = nullptr; d.tri_id_occ = nullptr;
+        }
+        s->build_ms = ms_all + ms_occ;
+        s->n_nodes = n - 1;
+    }
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
     *out = s;
     return PTB_OK;

@@ -69,7 +69,7 @@ static bool g_count_nodes = false;   // instrumented (untimed) run: count nodes 
 
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
-                            bool track, float *hit_t, int *hit_tri, cudaStream_t st) {
+                            bool track, float *hit_t, int *hit_tri, cudaStream_t st, const unsigned *order = nullptr) {
     ProfScope ps_(PK_CLOSEST, st);
     if (s->d.accel == PTB_ACCEL_LBVH) {
         const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
@@ -77,11 +77,11 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
             unsigned *work = q.work + (g_work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (track)
-                k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+                k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else if (g_count_nodes)
-                k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+                k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else
-                k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work);
+                k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
         } else if (track)
             k_closest_bvh32<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
         else if (g_count_nodes)
@@ -216,11 +216,13 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
     k_gen<float><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
     }
     PTB_LAUNCHED();
+    const bool sorting = d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic && s->sort_rays && q.sort.keys[0];
+    const unsigned *order = nullptr;       // visiting order of the live slots of queue `in` (null: slot order)
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
         const bool track = (b == 0) && !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
-        if ((rc = launch_closest32(s, q, in, q.count + b, N, track, q.hit_t, q.hit_tri, st))) return rc;
+        if ((rc = launch_closest32(s, q, in, q.count + b, N, track, q.hit_t, q.hit_tri, st, order))) return rc;
         if (track) {
             { ProfScope ps_(PK_RETRACE, st);
             k_retrace64<<<grid_for(N / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
@@ -230,17 +232,33 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         { ProfScope ps_(PK_SHADE, st);
         k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
-            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec);
+            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr);
         }
         PTB_LAUNCHED();
+        if (sorting) {      // order the survivors by the Morton key of their new origin (ptb_sort.cuh)
+            ProfScope ps_(PK_SORT, st);
+            const SortBufs &sb = q.sort;
+            const int blocks = (sb.tiles_max + PS_WARPS - 1) / PS_WARPS;
+            int cur = 0;
+            for (int pass = 0; pass < 3; ++pass) {
+                k_ps_hist<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist);
+                k_ps_rowscan<<<256, 1024, 0, st>>>(sb.ghist, sb.tiles_max, sb.totals);
+                k_ps_scatter<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass,
+                                                              sb.tiles_max, sb.ghist, sb.totals, sb.keys[cur ^ 1], sb.vals[cur ^ 1]);
+                g_launches += 3;
+                cur ^= 1;
+            }
+            order = sb.vals[1];     // 3 passes: 0 -> 1 -> 0 -> 1
+            PTB_LAUNCHED(); --g_launches;
+        }
         { ProfScope ps_(PK_SHADOW, st);
         if (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic) {
             unsigned *work = q.work + (g_work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (g_count_nodes)
-                k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work);
+                k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             else
-                k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work);
+                k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             PTB_LAUNCHED();
             k_nee_finish32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
         } else if (d.accel == PTB_ACCEL_LBVH) {

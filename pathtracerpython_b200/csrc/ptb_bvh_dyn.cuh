@@ -39,7 +39,7 @@ template <bool TRACK, bool COUNT>
 __global__ void __launch_bounds__(PTB_BVH_THREADS)
 k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__restrict__ qd, const unsigned *__restrict__ d_count,
                     float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
-                    unsigned *work) {
+                    unsigned *work, const unsigned *__restrict__ order) {
     const unsigned count = *d_count;
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
@@ -55,8 +55,8 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
             const bool want = ray == 0xffffffffu;
             const unsigned idx = claim_work(want, work, count);
             if (want && idx != 0xffffffffu) {
-                ray = idx;
-                const float4 a = qo[idx], b = qd[idx];
+                ray = order ? order[idx] : idx;
+                const float4 a = qo[ray], b = qd[ray];
                 o = mk3(a.x, a.y, a.z); d = mk3(b.x, b.y, b.z);
                 lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
                 h.t = 0.f; h.abs_t = 3.0e38f; h.slot = -1; best_ref = 0x7fffffff;
@@ -75,6 +75,10 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
             const float lim = TRACK ? h.abs_t + uc.best_dt : h.abs_t;
             const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
             bool go0 = (tn0 <= tf0) && (k0 <= lim), go1 = (tn1 <= tf1) && (k1 <= lim);
+            if (!TRACK) {   // a box the line leaves before |t| reaches the self-hit guard holds no acceptable hit (main.py:100)
+                go0 = go0 && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
+                go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
+            }
             const int c0 = n.d.x, c1 = n.d.y;
 #pragma unroll
             for (int side = 0; side < 2; ++side) {
@@ -132,7 +136,10 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
 template <bool COUNT>
 __global__ void __launch_bounds__(PTB_BVH_THREADS)
 k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const unsigned *__restrict__ d_count,
-                   int *__restrict__ sh_res, int cap, unsigned *work) {
+                   int *__restrict__ sh_res, int cap, unsigned *work, const unsigned *__restrict__ order) {
+    // occlusion tree: object triangles only (main.py:42); the full tree + min-ref pruning when it does not exist
+    const BvhNode *__restrict__ nodes = sc.nodes_occ ? sc.nodes_occ : sc.nodes;
+    const TriRec *__restrict__ tris = sc.nodes_occ ? sc.tri_occ : sc.tri;
     const unsigned paths = *d_count;
     const unsigned count = 3u * paths;
     unsigned nn = 0, nt = 0;
@@ -149,7 +156,8 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
             const unsigned idx = claim_work(want, work, count);
             if (want && idx != 0xffffffffu) {
                 item = idx;
-                const unsigned s = idx / paths, j = idx - s * paths;     // sample-major: neighbouring lanes, neighbouring paths
+                const unsigned s = idx / paths, jj = idx - s * paths;    // sample-major: neighbouring lanes, neighbouring paths
+                const unsigned j = order ? order[jj] : jj;
                 out_slot = s * (unsigned)cap + j;
                 const float4 pk = sh_p[j], dv = sh_d[out_slot];
                 o = mk3(pk.x, pk.y, pk.z); d = mk3(dv.x, dv.y, dv.z);
@@ -163,16 +171,17 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
         }
         if (!__any_sync(0xffffffffu, item != 0xffffffffu)) break;
         while (item != 0xffffffffu) {
-            const NodeBoxes n = ld_node(sc.nodes, node);
+            const NodeBoxes n = ld_node(nodes, node);
             if (COUNT) nn++;
             float tn0, tf0, tn1, tf1;
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
             slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
             const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
-            // subtrees matter only while they can still hold a triangle of an earlier object
+            // subtrees matter only while they can still hold a triangle of an earlier object, and only if the
+            // line is still inside them once |t| passes the self-occlusion guard (main.py:47-48)
             const int cut = min(found, sc.n_tri_obj);
-            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut);
-            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut);
+            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut) && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
+            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut) && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             const int c0 = n.d.x, c1 = n.d.y;
             bool finished = false;
 #pragma unroll
@@ -180,7 +189,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                 const bool go = side ? go1 : go0;
                 const int c = side ? c1 : c0;
                 if (go && c < 0) {
-                    const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + ~c);
+                    const float4 *tp = reinterpret_cast<const float4 *>(tris + ~c);
                     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
                     if (COUNT) nt++;
                     float t, dt; bool edge;

@@ -39,6 +39,12 @@ template <typename T> __device__ __forceinline__ T near_abs(T tn, T tf) {
     return (tn <= (T)0 && tf >= (T)0) ? (T)0 : (fabs(tn) < fabs(tf) ? fabs(tn) : fabs(tf));
 }
 
+// largest |t| of [tn, tf]
+template <typename T> __device__ __forceinline__ T far_abs(T tn, T tf) { return fabs(tn) > fabs(tf) ? fabs(tn) : fabs(tf); }
+// sqrt(1e-5) = 3.1623e-3 is the smallest |t| either query accepts (main.py:47-48, 100); boxes are padded and
+// the FP32 ray parameter carries ~1e-5 of error, so prune only below 3.0e-3
+#define PTB_TMIN_SAFE 3.0e-3f
+
 struct NodeBoxes { float4 a, b, c; int4 d; };
 __device__ __forceinline__ NodeBoxes ld_node(const BvhNode *nodes, int i) {
     const float4 *p = reinterpret_cast<const float4 *>(nodes + i);

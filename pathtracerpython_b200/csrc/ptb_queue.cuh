@@ -15,6 +15,7 @@
 //   per-path radiance                L[path id] = (r, g, b, -)         owned by one thread at a time
 #pragma once
 #include "ptb_isect.cuh"
+#include "ptb_sort.cuh"
 
 namespace ptb {
 
@@ -43,13 +44,16 @@ template <typename T> struct Queues {
     unsigned *count;       // [bounces + 2] live-path count entering each bounce
     unsigned *unc_count;   // number of uncertain primary rays
     int *unc_list;         // their queue positions
+    SortBufs sort;         // per-bounce re-ordering of the live slots (LBVH scenes, ptb_sort.cuh)
     int cap;               // paths per batch
 };
 
 template <typename T> inline size_t queue_bytes(size_t cap, int bounces) {
     size_t v = sizeof(typename VecT<T>::v4);
     size_t per = 4 * v + sizeof(T) + sizeof(int) + v + 3 * v + sizeof(int2) + v + sizeof(int) + 3 * sizeof(int);
-    return per * cap + 256 * 20 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
+    per += 4 * sizeof(unsigned);                                    // sort keys / values, ping-pong
+    const size_t tiles = (cap + PS_TILE - 1) / PS_TILE;
+    return per * cap + 256 * 28 + tiles * 256 * sizeof(unsigned) + 2048 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
 }
 
 // carve a workspace into queues; returns bytes used (0 if it does not fit)
@@ -68,6 +72,10 @@ template <typename T> inline size_t queue_carve(void *ws, size_t bytes, size_t c
     q.sh_aux = (int2 *)take(cap * sizeof(int2));
     q.unc_list = (int *)take(cap * sizeof(int));
     q.sh_res = (int *)take(3 * cap * sizeof(int));
+    for (int i = 0; i < 2; ++i) { q.sort.keys[i] = (unsigned *)take(cap * sizeof(unsigned)); q.sort.vals[i] = (unsigned *)take(cap * sizeof(unsigned)); }
+    q.sort.tiles_max = (int)((cap + PS_TILE - 1) / PS_TILE);
+    q.sort.ghist = (unsigned *)take((size_t)q.sort.tiles_max * 256 * sizeof(unsigned));
+    q.sort.totals = (unsigned *)take(256 * sizeof(unsigned));
     q.work = (unsigned *)take(256);
     q.count = (unsigned *)take((size_t)(bounces + 4) * sizeof(unsigned));
     q.unc_count = (unsigned *)take(4 * sizeof(unsigned));

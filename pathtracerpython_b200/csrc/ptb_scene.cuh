@@ -47,6 +47,7 @@ struct DScene {
     int accel;
     double eye[3], ortho[4], ambient, light_color[3];
     double light_total;       // sum(areas) (utils.py:30)
+    float bb_lo[3], bb_inv[3]; // scene box origin and 256 / extent: Morton sort keys of path origins (ptb_sort.cuh)
     unsigned long long *counters;   // device ptb_counters (first 8 u64) + queue counters
 };
 

@@ -104,7 +104,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
           const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
           unsigned *d_count_out, float4 *__restrict__ qo_out, float4 *__restrict__ qd_out,
           float4 *__restrict__ sh_p, float4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, float4 *__restrict__ L,
-          int cap, RecPtrs rec) {
+          int cap, RecPtrs rec, unsigned *__restrict__ sort_keys) {
     const unsigned count = *d_count_in;
     const float ex = (float)sc.eye[0], ey = (float)sc.eye[1], ez = (float)sc.eye[2];
     const float inv_npix = 1.0f / (float)bi.npix;
@@ -163,6 +163,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         }
         sh_p[j] = make_float4(P.x, P.y, P.z, k);
         sh_aux[j] = make_int2(id, tri);
+        if (sort_keys) sort_keys[j] = ps_key(P.x, P.y, P.z, sc.bb_lo, sc.bb_inv);
 
         // ---- bounce (main.py:240-264)
         const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, 3u);
