@@ -229,7 +229,7 @@ def run_ours(a):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     fp32_peak = _lib.fp32_peak_tflops() if hasattr(_lib, "fp32_peak_tflops") else None
     # dominant kernel of this rank
-    top = max(("closest_hit", "shadow", "shade"), key=lambda k: prof[k][0])
+    top = max(("closest_hit", "shadow", "shade", "bounce_fused"), key=lambda k: prof[k][0])
     n_tri, n_tri_obj = r.n_tri, int(flat["n_tri_obj"])
     t_top = prof[top][0] / 1e3
     info = r.info()
@@ -260,7 +260,13 @@ def run_ours(a):
                 "launches": prof[top][1], "avg_launch_ms": prof[top][0] / max(1, prof[top][1]), "kernel_ms": kernel_ms,
                 "note": "algorithmic bytes = 64 B per node fetched + 64 B per triangle record tested + ray/hit state (DESIGN.md)"}
     else:
-        if top == "closest_hit":
+        if top == "bounce_fused":
+            # one kernel per bounce: 3 shadow rays over the occlusion set + the next closest hit over all triangles
+            # (per-triangle formulation) + shading; the per-pixel primary rays (< 1 % of closest rays)
+            # are traced by the separate tracked kernel and are left in the count
+            flops = (ctr["shadow_rays"] * n_tri_obj + ctr["closest_rays"] * n_tri) * F_TEST + ctr["shaded"] * 400
+            bytes_ = ctr["shaded"] * (40 + 32) + ctr["closest_rays"] * 40
+        elif top == "closest_hit":
             flops = ctr["closest_rays"] * n_tri * F_TEST
             bytes_ = ctr["closest_rays"] * RAY_STATE_BYTES["closest_hit"]
         elif top == "shadow":

@@ -69,7 +69,9 @@ typedef struct {
 enum { PTB_PREC_FP32 = 0, PTB_PREC_FP64 = 1 };
 enum {
     PTB_FLAG_NO_FP64_RETRACE = 1,   /* FP32 only: skip the FP64 re-trace of uncertain primary hits */
-    PTB_FLAG_SHARE_PRIMARY = 2,     /* trace the (identical, main.py:191) primary ray once per pixel */
+    PTB_FLAG_SEPARATE_KERNELS = 2,  /* A/B and test switch: one primary ray per SAMPLE (default: once per pixel, they are
+                                       identical, main.py:191) and, for small scenes, the separate shade / shadow /
+                                       closest-hit kernels instead of the fused per-bounce kernel */
     PTB_FLAG_COUNT_NODES = 4        /* instrumented run: count LBVH nodes visited / triangles tested */
 };
 
@@ -149,10 +151,11 @@ int ptb_scatter_accum(const ptb_pixels *px, const float *d_accum_shard, float *d
 
 /* Per-kernel-class device timing (CUDA events on the launch stream), for the roofline report.
  * kinds: 0 camera rays, 1 closest-hit, 2 FP64 re-trace, 3 shade/bounce, 4 shadow/any-hit + NEE,
- * 5 batch reduce, 6 tone map, 7 other, 8 LBVH build, 9 per-bounce ray sort.  ptb_profile_read synchronises the device,
+ * 5 batch reduce, 6 tone map, 7 other, 8 LBVH build, 9 per-bounce ray sort,
+ * 10 fused per-bounce kernel (shade + shadow + next closest hit, small scenes).  ptb_profile_read synchronises the device,
  * writes the accumulated milliseconds and launch counts per kind (arrays of PTB_PROF_KINDS) and
  * clears the accumulators. */
-#define PTB_PROF_KINDS 10
+#define PTB_PROF_KINDS 11
 int ptb_profile_enable(int on);
 int ptb_profile_read(double *ms_per_kind, uint64_t *launches_per_kind);
 

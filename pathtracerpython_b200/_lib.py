@@ -8,7 +8,7 @@ LIB_PATH = os.path.join(_HERE, "libptb.so")
 
 PREC_FP32, PREC_FP64 = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
-FLAG_NO_FP64_RETRACE, FLAG_SHARE_PRIMARY, FLAG_COUNT_NODES = 1, 2, 4
+FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES = 1, 2, 4
 
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
@@ -48,7 +48,7 @@ class Counters(C.Structure):
                                           "nodes_visited", "tris_tested", "nodes_visited_shadow", "tris_tested_shadow")]
 
 
-PROF_KINDS = ["camera", "closest_hit", "fp64_retrace", "shade", "shadow", "reduce", "tonemap", "other", "bvh_build", "ray_sort"]
+PROF_KINDS = ["camera", "closest_hit", "fp64_retrace", "shade", "shadow", "reduce", "tonemap", "other", "bvh_build", "ray_sort", "bounce_fused"]
 
 _lib = None
 

@@ -12,6 +12,7 @@
 #include "ptb_bvh_build.cuh"
 #include "ptb_bvh_kernels.cuh"
 #include "ptb_bvh_dyn.cuh"
+#include "ptb_fused.cuh"
 
 namespace ptb {
 
@@ -43,7 +44,7 @@ static int grid_for(size_t work, int threads, int blocks_per_sm) {
 }
 
 // ---- optional per-kernel-class timing with CUDA events on the launch stream
-enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD, PK_SORT };
+enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD, PK_SORT, PK_BOUNCE };
 struct ProfRec { int kind; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;

@@ -212,27 +212,64 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
     int rc;
     const size_t N = (size_t)bi.npix * bi.S;
     const DScene &d = s->d;
+    const bool separate = (p->flags & PTB_FLAG_SEPARATE_KERNELS) != 0;
+    const bool share = !separate && p->bounces > 0;     // one primary ray + hit per pixel, read by all S samples (A-Q14)
+    const bool fused = share && d.accel == PTB_ACCEL_BRUTE && s->use_planes;
     { ProfScope ps_(PK_GEN, st);
-    k_gen<float><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
+    if (share)
+        k_gen_pixels<<<grid_for(fused ? (size_t)bi.npix : N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, fused ? 0 : 1, q.count, q.unc_count, p->bounces + 2);
+    else
+        k_gen<float><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
     }
     PTB_LAUNCHED();
+    const size_t n_primary = share ? (size_t)bi.npix : N;
+    if (fused) {        // ptb_fused.cuh: one kernel per bounce, geometry in shared memory
+        const bool track = !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
+        if ((rc = launch_closest32(s, q, 0, q.count, n_primary, track, q.hit_t, q.hit_tri, st))) return rc;
+        if (track) {
+            { ProfScope ps_(PK_RETRACE, st);
+            k_retrace64<<<grid_for(n_primary / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
+            }
+            PTB_LAUNCHED();
+        }
+        float *ht[2] = {q.hit_t, q.hit_t2}; int *hr[2] = {q.hit_tri, q.hit_tri2};
+        const size_t smem = plane_smem_bytes(s->planes.n_planes);
+        for (int b = 0; b < p->bounces; ++b) {
+            const int in = b & 1, out = in ^ 1;
+            bi.bounce = b;
+            const int last = b == p->bounces - 1;
+            ProfScope ps_(PK_BOUNCE, st);
+            if (b == 0)
+                k_bounce_planes32<true><<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, smem, st>>>(
+                    d, s->planes, bi, q.qo[0], q.qd[0], ht[0], hr[0], q.count, q.count + 1, q.qo[1], q.qd[1], ht[1], hr[1], q.L, last, rec);
+            else
+                k_bounce_planes32<false><<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, smem, st>>>(
+                    d, s->planes, bi, q.qo[in], q.qd[in], ht[in], hr[in], q.count + b, q.count + b + 1, q.qo[out], q.qd[out], ht[out], hr[out], q.L, last, rec);
+            PTB_LAUNCHED();
+        }
+        { ProfScope ps_(PK_REDUCE, st);
+        k_reduce<float><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+        }
+        PTB_LAUNCHED();
+        return PTB_OK;
+    }
     const bool sorting = d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic && s->sort_rays && q.sort.keys[0];
     const unsigned *order = nullptr;       // visiting order of the live slots of queue `in` (null: slot order)
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
         const bool track = (b == 0) && !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
-        if ((rc = launch_closest32(s, q, in, q.count + b, N, track, q.hit_t, q.hit_tri, st, order))) return rc;
+        if ((rc = launch_closest32(s, q, in, q.count + b, b == 0 ? n_primary : N, track, q.hit_t, q.hit_tri, st, order))) return rc;
         if (track) {
             { ProfScope ps_(PK_RETRACE, st);
-            k_retrace64<<<grid_for(N / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
+            k_retrace64<<<grid_for(n_primary / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
             }
             PTB_LAUNCHED();
         }
         { ProfScope ps_(PK_SHADE, st);
         k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
-            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr);
+            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr, (share && b == 0) ? 1 : 0);
         }
         PTB_LAUNCHED();
         if (sorting) {      // order the survivors by the Morton key of their new origin (ptb_sort.cuh)

@@ -53,6 +53,36 @@ __device__ __forceinline__ float bary_min(const float4 q1, const float4 q2, floa
 #define PTB_TMIN_F 3.1622776e-3f   // sqrt(1e-5): |t| threshold equivalent to squared_dist > ZERO
 
 // ---------------------------------------------------------------- closest hit
+// Warp-collective (votes): all 32 lanes must call it together; lanes with live == false never keep a group alive.
+__device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_planes, const float4 a, const float4 b, bool live,
+                                                 float &best_t, int &best_ref) {
+    float best_a = live ? 3.0e38f : 0.f;
+    best_t = 0.f;
+    best_ref = -1;
+    for (int g = 0; g < n_planes; ++g) {
+        const float4 nd = planes[g].nd;
+        const float dn = fmaf(nd.z, b.z, fmaf(nd.y, b.y, nd.x * b.x));
+        const float on = nd.w - fmaf(nd.z, a.z, fmaf(nd.y, a.y, nd.x * a.x));
+        const float t = on * rcp_approx(dn);
+        const float at = fabsf(t);
+        const bool ok = (fabsf(dn) > PTB_ZERO_F) && (at > PTB_TMIN_F) && (at < best_a);
+        if (!__any_sync(0xffffffffu, ok)) continue;
+        const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
+        if (planes[g].kind) {                   // warp-uniform
+            float u;
+            if (para_hit(planes[g].a1, planes[g].a2, px, py, pz, u) && ok) {
+                best_a = at; best_t = t; best_ref = u > 0.0f ? planes[g].ref_a : planes[g].ref_b;
+            }
+        } else {
+            const float ma = bary_min(planes[g].a1, planes[g].a2, px, py, pz);
+            const float mb = bary_min(planes[g].b1, planes[g].b2, px, py, pz);
+            // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
+            const bool ha = ok && ma > 0.0f, hb = ok && mb > 0.0f;
+            if (ha || hb) { best_a = at; best_t = t; best_ref = ha ? planes[g].ref_a : planes[g].ref_b; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(PTB_TRACE_THREADS)
 k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
                    const unsigned *__restrict__ d_count, float *__restrict__ hit_t, int *__restrict__ hit_tri) {
@@ -60,41 +90,70 @@ k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, cons
     const PlaneRec *planes = stage_planes(smem_raw, ps);
     const unsigned count = *d_count;
     const unsigned stride = gridDim.x * blockDim.x;
-    // whole warps iterate together so the votes below are legal
+    // whole warps iterate together so the votes are legal
     const unsigned count_w = (count + 31u) & ~31u;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count_w; i += stride) {
         const bool live = i < count;
         const float4 a = live ? qo[i] : make_float4(0, 0, 0, 0), b = live ? qd[i] : make_float4(1, 0, 0, 0);
-        float best_a = live ? 3.0e38f : 0.f, best_t = 0.f;
-        int best_ref = -1;
-        for (int g = 0; g < ps.n_planes; ++g) {
-            const float4 nd = planes[g].nd;
-            const float dn = fmaf(nd.z, b.z, fmaf(nd.y, b.y, nd.x * b.x));
-            const float on = nd.w - fmaf(nd.z, a.z, fmaf(nd.y, a.y, nd.x * a.x));
-            const float t = on * rcp_approx(dn);
-            const float at = fabsf(t);
-            const bool ok = (fabsf(dn) > PTB_ZERO_F) && (at > PTB_TMIN_F) && (at < best_a);
-            if (!__any_sync(0xffffffffu, ok)) continue;
-            const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
-            if (planes[g].kind) {                   // warp-uniform
-                float u;
-                if (para_hit(planes[g].a1, planes[g].a2, px, py, pz, u) && ok) {
-                    best_a = at; best_t = t; best_ref = u > 0.0f ? planes[g].ref_a : planes[g].ref_b;
-                }
-            } else {
-                const float ma = bary_min(planes[g].a1, planes[g].a2, px, py, pz);
-                const float mb = bary_min(planes[g].b1, planes[g].b2, px, py, pz);
-                // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
-                const bool ha = ok && ma > 0.0f, hb = ok && mb > 0.0f;
-                if (ha || hb) { best_a = at; best_t = t; best_ref = ha ? planes[g].ref_a : planes[g].ref_b; }
-            }
-        }
+        float best_t; int best_ref;
+        closest_planes32(planes, ps.n_planes, a, b, live, best_t, best_ref);
         if (live) {
             hit_t[i] = best_t;
             hit_tri[i] = best_ref;
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(sc.counters + CTR_CLOSEST, (unsigned long long)count);
+}
+
+// ---------------------------------------------------------------- occlusion of the 3 light samples of one path
+// Warp-collective.  pk.xyz = shaded point, d0..d2 = unit directions (w = squared distance to the light
+// sample).  occ0 / occ1: sample occluded; leak_ref: lowest reference index among the occluders of sample
+// 2, 0x7fffffff if it is unoccluded (-1 for dead lanes).
+__device__ __forceinline__ void shadow_planes32(const PlaneRec *planes, int n_occ, const float4 pk, const float4 d0, const float4 d1,
+                                                const float4 d2, bool live, bool &occ0, bool &occ1, int &leak_ref) {
+    occ0 = !live; occ1 = !live;            // dead lanes never keep a group alive
+    leak_ref = live ? 0x7fffffff : -1;     // lowest reference index among occluders of sample 2
+    for (int g = 0; g < n_occ; ++g) {
+        const float4 nd = planes[g].nd;
+        const float on = nd.w - fmaf(nd.z, pk.z, fmaf(nd.y, pk.y, nd.x * pk.x));
+        const float dn0 = fmaf(nd.z, d0.z, fmaf(nd.y, d0.y, nd.x * d0.x));
+        const float dn1 = fmaf(nd.z, d1.z, fmaf(nd.y, d1.y, nd.x * d1.x));
+        const float dn2 = fmaf(nd.z, d2.z, fmaf(nd.y, d2.y, nd.x * d2.x));
+        const float t0 = on * rcp_approx(dn0), t1 = on * rcp_approx(dn1), t2 = on * rcp_approx(dn2);
+        const float s0 = t0 * t0, s1 = t1 * t1, s2 = t2 * t2;
+        // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
+        const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w);
+        const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w);
+        const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
+        if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
+        const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
+        const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);
+        const float p2x = fmaf(t2, d2.x, pk.x), p2y = fmaf(t2, d2.y, pk.y), p2z = fmaf(t2, d2.z, pk.z);
+        const float4 a1 = planes[g].a1, a2 = planes[g].a2;
+        if (planes[g].kind) {                  // warp-uniform: parallelogram pair, both triangles in the occlusion set
+            float u0, u1, u2;
+            const bool h0 = para_hit(a1, a2, p0x, p0y, p0z, u0);
+            const bool h1 = para_hit(a1, a2, p1x, p1y, p1z, u1);
+            const bool h2 = para_hit(a1, a2, p2x, p2y, p2z, u2);
+            occ0 = occ0 || (ok0 && h0);
+            occ1 = occ1 || (ok1 && h1);
+            if (ok2 && h2) leak_ref = min(leak_ref, u2 > 0.0f ? planes[g].ref_a : planes[g].ref_b);
+        } else {
+            const bool ha0 = bary_min(a1, a2, p0x, p0y, p0z) > 0.0f;
+            const bool ha1 = bary_min(a1, a2, p1x, p1y, p1z) > 0.0f;
+            const bool ha2 = bary_min(a1, a2, p2x, p2y, p2z) > 0.0f;
+            bool hb0 = false, hb1 = false, hb2 = false;
+            if (planes[g].n_obj > 1) {             // warp-uniform
+                const float4 b1 = planes[g].b1, b2 = planes[g].b2;
+                hb0 = bary_min(b1, b2, p0x, p0y, p0z) > 0.0f;
+                hb1 = bary_min(b1, b2, p1x, p1y, p1z) > 0.0f;
+                hb2 = bary_min(b1, b2, p2x, p2y, p2z) > 0.0f;
+            }
+            occ0 = occ0 || (ok0 && (ha0 || hb0));
+            occ1 = occ1 || (ok1 && (ha1 || hb1));
+            if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
+        }
+    }
 }
 
 // ---------------------------------------------------------------- shadow rays + NEE accumulation
@@ -114,49 +173,8 @@ k_shadow_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ sh_p, con
         const unsigned jj = live ? j : 0u;
         const float4 pk = sh_p[jj];
         const float4 d0 = sh_d[jj], d1 = sh_d[(size_t)cap + jj], d2 = sh_d[2 * (size_t)cap + jj];
-        bool occ0 = !live, occ1 = !live;       // dead lanes never keep a group alive
-        int leak_ref = live ? 0x7fffffff : -1; // lowest reference index among occluders of sample 2
-        for (int g = 0; g < ps.n_occ; ++g) {
-            const float4 nd = planes[g].nd;
-            const float on = nd.w - fmaf(nd.z, pk.z, fmaf(nd.y, pk.y, nd.x * pk.x));
-            const float dn0 = fmaf(nd.z, d0.z, fmaf(nd.y, d0.y, nd.x * d0.x));
-            const float dn1 = fmaf(nd.z, d1.z, fmaf(nd.y, d1.y, nd.x * d1.x));
-            const float dn2 = fmaf(nd.z, d2.z, fmaf(nd.y, d2.y, nd.x * d2.x));
-            const float t0 = on * rcp_approx(dn0), t1 = on * rcp_approx(dn1), t2 = on * rcp_approx(dn2);
-            const float s0 = t0 * t0, s1 = t1 * t1, s2 = t2 * t2;
-            // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
-            const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w);
-            const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w);
-            const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
-            if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
-            const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
-            const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);
-            const float p2x = fmaf(t2, d2.x, pk.x), p2y = fmaf(t2, d2.y, pk.y), p2z = fmaf(t2, d2.z, pk.z);
-            const float4 a1 = planes[g].a1, a2 = planes[g].a2;
-            if (planes[g].kind) {                  // warp-uniform: parallelogram pair, both triangles in the occlusion set
-                float u0, u1, u2;
-                const bool h0 = para_hit(a1, a2, p0x, p0y, p0z, u0);
-                const bool h1 = para_hit(a1, a2, p1x, p1y, p1z, u1);
-                const bool h2 = para_hit(a1, a2, p2x, p2y, p2z, u2);
-                occ0 = occ0 || (ok0 && h0);
-                occ1 = occ1 || (ok1 && h1);
-                if (ok2 && h2) leak_ref = min(leak_ref, u2 > 0.0f ? planes[g].ref_a : planes[g].ref_b);
-            } else {
-                const bool ha0 = bary_min(a1, a2, p0x, p0y, p0z) > 0.0f;
-                const bool ha1 = bary_min(a1, a2, p1x, p1y, p1z) > 0.0f;
-                const bool ha2 = bary_min(a1, a2, p2x, p2y, p2z) > 0.0f;
-                bool hb0 = false, hb1 = false, hb2 = false;
-                if (planes[g].n_obj > 1) {             // warp-uniform
-                    const float4 b1 = planes[g].b1, b2 = planes[g].b2;
-                    hb0 = bary_min(b1, b2, p0x, p0y, p0z) > 0.0f;
-                    hb1 = bary_min(b1, b2, p1x, p1y, p1z) > 0.0f;
-                    hb2 = bary_min(b1, b2, p2x, p2y, p2z) > 0.0f;
-                }
-                occ0 = occ0 || (ok0 && (ha0 || hb0));
-                occ1 = occ1 || (ok1 && (ha1 || hb1));
-                if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
-            }
-        }
+        bool occ0, occ1; int leak_ref;
+        shadow_planes32(planes, ps.n_occ, pk, d0, d1, d2, live, occ0, occ1, leak_ref);
         if (!live) continue;
         const int2 aux = sh_aux[j];
         const float4 sn = __ldg(sc.tri_sn + aux.y);

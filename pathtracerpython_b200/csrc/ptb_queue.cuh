@@ -36,6 +36,8 @@ template <typename T> struct Queues {
     v4 *qo[2], *qd[2];     // ping-pong ray queues
     T *hit_t;
     int *hit_tri;
+    T *hit_t2;             // second hit record set: the fused per-bounce kernel writes hits of the NEXT queue
+    int *hit_tri2;
     v4 *sh_p, *sh_d;       // sh_d is [3][cap]
     int2 *sh_aux;
     int *sh_res;           // [3][cap] LBVH shadow outcome per (light sample, path): occluding object or -1
@@ -52,8 +54,9 @@ template <typename T> inline size_t queue_bytes(size_t cap, int bounces) {
     size_t v = sizeof(typename VecT<T>::v4);
     size_t per = 4 * v + sizeof(T) + sizeof(int) + v + 3 * v + sizeof(int2) + v + sizeof(int) + 3 * sizeof(int);
     per += 4 * sizeof(unsigned);                                    // sort keys / values, ping-pong
+    per += sizeof(T) + sizeof(int);                                 // second hit record set
     const size_t tiles = (cap + PS_TILE - 1) / PS_TILE;
-    return per * cap + 256 * 28 + tiles * 256 * sizeof(unsigned) + 2048 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
+    return per * cap + 256 * 32 + tiles * 256 * sizeof(unsigned) + 2048 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
 }
 
 // carve a workspace into queues; returns bytes used (0 if it does not fit)
@@ -69,6 +72,8 @@ template <typename T> inline size_t queue_carve(void *ws, size_t bytes, size_t c
     q.L = (v4 *)take(cap * sizeof(v4));
     q.hit_t = (T *)take(cap * sizeof(T));
     q.hit_tri = (int *)take(cap * sizeof(int));
+    q.hit_t2 = (T *)take(cap * sizeof(T));
+    q.hit_tri2 = (int *)take(cap * sizeof(int));
     q.sh_aux = (int2 *)take(cap * sizeof(int2));
     q.unc_list = (int *)take(cap * sizeof(int));
     q.sh_res = (int *)take(3 * cap * sizeof(int));

@@ -99,14 +99,68 @@ __device__ __forceinline__ float pow_small_int(float x, int n) {
     return r;
 }
 
+// The 3 light samples of one shaded point (main.py:30-40, utils.py:21-46): unit direction to the sampled
+// light point in xyz, squared distance in w.  Philox dims 4s .. 4s+3.
+__device__ __forceinline__ void light_samples32(const DScene &sc, uint32_t seed, uint32_t r, uint32_t sample, uint32_t bounce,
+                                                const f3 P, float4 (&out)[3]) {
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const uint4 w = rng4(seed, r, sample, bounce, (uint32_t)s);
+        const int li = pick_light_int(sc.light_thr, sc.n_light_tri, w.x >> 8);
+        const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
+        const float inv = rcp_approx((c0 + c1) + c2);
+        const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
+        const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
+        const f3 v = mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)) - P.x,
+                         fmaf(wc, v3.y, fmaf(wb, v2.y, wa * v1.y)) - P.y,
+                         fmaf(wc, v3.z, fmaf(wb, v2.z, wa * v1.z)) - P.z);
+        const float d2 = dot(v, v);
+        const float rn = rsqrtf(d2);
+        out[s] = make_float4(v.x * rn, v.y * rn, v.z * rn, d2);
+    }
+}
+
+// The bounce step (main.py:240-264): lobe pick, new direction wv, new accumulated_k.  Philox dims 12-14.
+__device__ __forceinline__ void bounce32(const DScene &sc, uint32_t seed, uint32_t r, uint32_t sample, uint32_t bounce, int obj,
+                                         const f3 n, const f3 d, const f3 P, float k, f3 &wv, float &knew, bool &diffuse) {
+    const uint4 w = rng4(seed, r, sample, bounce, 3u);
+    diffuse = (int)(w.x >> 8) < __ldg(sc.obj_lobe_thr + obj);
+    const float cy = n.y, sy = sqrtf(fmaxf(0.f, fmaf(-cy, cy, 1.0f)));   // cos / sin of arccos(n.y)
+    f3 v;
+    if (diffuse) {
+        const float u1 = u01<float>(w.y), u2 = u01<float>(w.z);
+        const float sp = sqrtf(1.0f - u1), cp = sqrtf(u1);               // sin / cos of arccos(sqrt(u1))
+        float st, ct;
+        sincosf(6.28f * u2, &st, &ct);                                   // TAU = 6.28 (main.py:19)
+        v = mk3(sp * ct, sp * st, cp);
+    } else {
+        const float dn2 = 2.0f * dot(n, d);
+        v = mk3(fmaf(dn2, n.x, -d.x), fmaf(dn2, n.y, -d.y), fmaf(dn2, n.z, -d.z));
+        const float rn = rsqrtf(dot(v, v));
+        v = v * rn;
+    }
+    wv = mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));   // R_y(arccos(n.y)) (main.py:148-162)
+    if (diffuse) {
+        knew = k * (__ldg(sc.mat32 + 8 * obj + 4) * dot(wv, n));
+    } else {
+        f3 e = mk3((float)sc.eye[0] - P.x, (float)sc.eye[1] - P.y, (float)sc.eye[2] - P.z);
+        e = e * rsqrtf(dot(e, e));
+        const int pn = __ldg(sc.obj_pow_int + obj);
+        const float ew = dot(e, wv);
+        const float pw = pn >= 0 ? pow_small_int(ew, pn) : powf(ew, __ldg(sc.mat32 + 8 * obj + 7));
+        knew = k * (__ldg(sc.mat32 + 8 * obj + 5) * pw);
+    }
+}
+
 __global__ void __launch_bounds__(PTB_SHADE_THREADS)
 k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
           const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
           unsigned *d_count_out, float4 *__restrict__ qo_out, float4 *__restrict__ qd_out,
           float4 *__restrict__ sh_p, float4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, float4 *__restrict__ L,
-          int cap, RecPtrs rec, unsigned *__restrict__ sort_keys) {
-    const unsigned count = *d_count_in;
-    const float ex = (float)sc.eye[0], ey = (float)sc.eye[1], ez = (float)sc.eye[2];
+          int cap, RecPtrs rec, unsigned *__restrict__ sort_keys, int share_primary) {
+    // share_primary (bounce 0 only): every sample of a pixel starts with the same primary ray (main.py:191,
+    // A-Q14), so the ray and its closest hit are stored once per pixel slot and read by all S samples
+    const unsigned count = share_primary ? (unsigned)bi.npix * (unsigned)bi.S : *d_count_in;
     const float inv_npix = 1.0f / (float)bi.npix;
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
         const unsigned i = base + threadIdx.x;
@@ -114,8 +168,10 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         float4 a, b; float t = 0.f; int tri = -1, id = 0, obj = 0;
         float4 sn = make_float4(0, 0, 0, 0);
         if (i < count) {
-            a = qo[i]; b = qd[i]; t = hit_t[i]; tri = hit_tri[i];
-            id = id_unpack(b.w);
+            unsigned src = i;
+            if (share_primary) { int q_, r_; fast_divmod((int)i, bi.npix, inv_npix, q_, r_); src = (unsigned)r_; }
+            a = qo[src]; b = qd[src]; t = hit_t[src]; tri = hit_tri[src];
+            id = share_primary ? (int)i : id_unpack(b.w);
             if (tri >= 0) {
                 sn = __ldg(sc.tri_sn + tri);
                 obj = __float_as_int(sn.w);
@@ -146,53 +202,17 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
 
         // ---- 3 light samples (main.py:30-40)
+        float4 ld[3];
+        light_samples32(sc, bi.seed, r, sample, (uint32_t)bi.bounce, P, ld);
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
-            const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);
-            const int li = pick_light_int(sc.light_thr, sc.n_light_tri, w.x >> 8);
-            const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
-            const float inv = rcp_approx((c0 + c1) + c2);
-            const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
-            const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
-            const f3 v = mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)) - P.x,
-                             fmaf(wc, v3.y, fmaf(wb, v2.y, wa * v1.y)) - P.y,
-                             fmaf(wc, v3.z, fmaf(wb, v2.z, wa * v1.z)) - P.z);
-            const float d2 = dot(v, v);
-            const float rn = rsqrtf(d2);
-            sh_d[(size_t)s * cap + j] = make_float4(v.x * rn, v.y * rn, v.z * rn, d2);
-        }
+        for (int s = 0; s < 3; ++s) sh_d[(size_t)s * cap + j] = ld[s];
         sh_p[j] = make_float4(P.x, P.y, P.z, k);
         sh_aux[j] = make_int2(id, tri);
         if (sort_keys) sort_keys[j] = ps_key(P.x, P.y, P.z, sc.bb_lo, sc.bb_inv);
 
         // ---- bounce (main.py:240-264)
-        const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, 3u);
-        const bool diffuse = (int)(w.x >> 8) < __ldg(sc.obj_lobe_thr + obj);
-        const float cy = n.y, sy = sqrtf(fmaxf(0.f, fmaf(-cy, cy, 1.0f)));   // cos / sin of arccos(n.y)
-        f3 v; float knew;
-        if (diffuse) {
-            const float u1 = u01<float>(w.y), u2 = u01<float>(w.z);
-            const float sp = sqrtf(1.0f - u1), cp = sqrtf(u1);               // sin / cos of arccos(sqrt(u1))
-            float st, ct;
-            sincosf(6.28f * u2, &st, &ct);                                   // TAU = 6.28 (main.py:19)
-            v = mk3(sp * ct, sp * st, cp);
-        } else {
-            const float dn2 = 2.0f * dot(n, d);
-            v = mk3(fmaf(dn2, n.x, -d.x), fmaf(dn2, n.y, -d.y), fmaf(dn2, n.z, -d.z));
-            const float rn = rsqrtf(dot(v, v));
-            v = v * rn;
-        }
-        const f3 wv = mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));   // R_y(arccos(n.y)) (main.py:148-162)
-        if (diffuse) {
-            knew = k * (__ldg(sc.mat32 + 8 * obj + 4) * dot(wv, n));
-        } else {
-            f3 e = mk3(ex - P.x, ey - P.y, ez - P.z);
-            e = e * rsqrtf(dot(e, e));
-            const int pn = __ldg(sc.obj_pow_int + obj);
-            const float ew = dot(e, wv);
-            const float pw = pn >= 0 ? pow_small_int(ew, pn) : powf(ew, __ldg(sc.mat32 + 8 * obj + 7));
-            knew = k * (__ldg(sc.mat32 + 8 * obj + 5) * pw);
-        }
+        f3 wv; float knew; bool diffuse;
+        bounce32(sc, bi.seed, r, sample, (uint32_t)bi.bounce, obj, n, d, P, k, wv, knew, diffuse);
         qo_out[j] = make_float4(P.x, P.y, P.z, knew);
         qd_out[j] = make_float4(wv.x, wv.y, wv.z, __int_as_float(id));
         if (rec.any) {

@@ -96,6 +96,21 @@ def test_tessellated_2048_vs_oracle(tess8):
     r.close()
 
 
+def test_lbvh_reordered_shared_primary_equals_plain_pipeline(tess8):
+    """Per-bounce Morton re-ordering and the per-pixel primary ray only change WHERE a ray is processed, never
+    its arithmetic: radiance and records are bit-identical to the plain pipeline (one primary ray per sample)."""
+    import torch
+    r = ptb.Renderer(tess8, device=0)
+    a, ra = r.trace_paths(3, 4, seed=13, width=96, height=96, records=True)
+    b, rb = r.trace_paths(3, 4, seed=13, width=96, height=96, records=True, flags=ptb.FLAG_SEPARATE_KERNELS)
+    assert torch.equal(a, b)
+    for k in ra:
+        assert torch.equal(ra[k], rb[k]), k
+    c, _ = r.trace_paths(3, 4, seed=13, width=96, height=96, samples_per_batch=1)
+    assert torch.equal(a, c)
+    r.close()
+
+
 def test_tessellation_keeps_the_hit_object(cornell):
     n = 24                                             # 18 432 triangles
     t = synth.tessellate(cornell, n)

@@ -132,6 +132,8 @@ def test_paths_vs_c_oracle_larger(rnd, flat, res, spp, nb):
     ok = _signature_match(rec, ref)
     assert (~ok & live).sum() / live.sum() < 2e-5
     assert np.abs(rec["contrib64"] - ref["contrib"])[ok].max() < 1e-9
+    c = rnd.counters(reset=True)       # FP64 mode traces every sample's primary ray, like the reference
+    assert abs(c["closest_rays"] - ref["closest_rays"]) <= 0.01 * ref["closest_rays"]
     # FP32 mode
     accum, rec = rnd.trace_paths(spp, nb, seed=1234, width=res, height=res, records=True)
     rec = {k: v.cpu().numpy() for k, v in rec.items()}
@@ -139,9 +141,12 @@ def test_paths_vs_c_oracle_larger(rnd, flat, res, spp, nb):
     divergent = (~ok & live).sum() / live.sum()
     assert divergent < 1e-3, divergent
     assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
-    # counters agree with the oracle's ray census up to the divergent paths
+    # counters agree with the oracle's ray census up to the divergent paths; the product traces the primary ray
+    # once per pixel (all samples share it, main.py:191), so (spp - 1) primary rays per pixel are not traced
     c = rnd.counters(reset=True)
-    assert abs(c["closest_rays"] / 2 - ref["closest_rays"]) <= 0.01 * ref["closest_rays"]
+    want = ref["closest_rays"] - res * res * (spp - 1)
+    assert abs(c["closest_rays"] - want) <= 0.01 * want
+    assert abs(c["shadow_rays"] - ref["shadow_rays"]) <= 0.01 * ref["shadow_rays"]
 
 
 # ------------------------------------------------------------------ check 3
@@ -181,6 +186,30 @@ def test_shards_partition_the_frame_bitwise(rnd):
         px, _ = rnd.pixels(res, res, s, 3, 100)
         rnd.scatter(px, part, merged)
     assert torch.equal(full, merged)
+
+
+@pytest.mark.parametrize("res,spp,nb", [(40, 3, 1), (40, 2, 4), (200, 5, 5)])
+def test_fused_bounce_kernel_equals_separate_kernels(rnd, res, spp, nb):
+    """The per-bounce fused kernel + one primary ray per pixel (the product path for small scenes) and the
+    separate shade / shadow / closest-hit kernels with one primary ray per sample run the same arithmetic in the
+    same order: radiance and every per-path record must be bit-identical."""
+    import torch
+    a, ra = rnd.trace_paths(spp, nb, seed=21, width=res, height=res, records=True)
+    b, rb = rnd.trace_paths(spp, nb, seed=21, width=res, height=res, records=True, flags=ptb.FLAG_SEPARATE_KERNELS)
+    assert torch.equal(a, b)
+    for k in ra:
+        assert torch.equal(ra[k], rb[k]), k
+    # and without records (the kernel skips the last bounce's unused direction then)
+    a2, _ = rnd.trace_paths(spp, nb, seed=21, width=res, height=res)
+    assert torch.equal(a, a2)
+    # several batches
+    a3, _ = rnd.trace_paths(spp, nb, seed=21, width=res, height=res, samples_per_batch=2)
+    assert torch.equal(a, a3)
+
+
+def test_zero_bounces_is_black(rnd):
+    a, _ = rnd.trace_paths(2, 0, seed=1)
+    assert float(a[:, :3].abs().max()) == 0.0 and float(a[:, 3].min()) == 2.0
 
 
 def test_sample_ranges_and_batches_compose(rnd):
