@@ -25,6 +25,10 @@
 
 namespace ptb {
 
+#ifndef PTB_FUSED_MIN_BLOCKS
+#define PTB_FUSED_MIN_BLOCKS 4
+#endif
+
 // camera rays for the pixel set only (S samples share them); count[0] = npix drives the closest-hit kernel
 __global__ void __launch_bounds__(256)
 k_gen_pixels(DScene sc, BatchInfo bi, float4 *__restrict__ qo, float4 *__restrict__ qd, float4 *__restrict__ L, int zero_L,
@@ -53,7 +57,7 @@ k_gen_pixels(DScene sc, BatchInfo bi, float4 *__restrict__ qo, float4 *__restric
 // FIRST: bounce 0 - items are all npix x S paths, ray / hit read per pixel slot, L written (not updated).
 // Otherwise items are the compacted paths whose previous ray hit an object.
 template <bool FIRST>
-__global__ void __launch_bounds__(PTB_SHADE_THREADS)
+__global__ void __launch_bounds__(PTB_SHADE_THREADS, PTB_FUSED_MIN_BLOCKS)
 k_bounce_planes32(DScene sc, PlaneScene ps, BatchInfo bi, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
                   const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
                   unsigned *d_count_out, float4 *__restrict__ qo_out, float4 *__restrict__ qd_out, float *__restrict__ hit_t_out,
