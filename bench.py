@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--res", type=int, default=1024)
+    ap.add_argument("--width", type=int, default=0, help="frame width (default: --res)")
+    ap.add_argument("--height", type=int, default=0, help="frame height (default: --res); config 5 is 3840 x 2160")
     ap.add_argument("--spp", type=int, default=1024)
     ap.add_argument("--bounces", type=int, default=5)
     ap.add_argument("--scene", default=None)
@@ -43,12 +45,14 @@ def parse():
     ap.add_argument("--shard", default="tile", choices=["tile", "sample"], help="multi-GPU partition (SURVEY.md 8e)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the bounded baseline sample")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.width, a.height = a.width or a.res, a.height or a.res
+    return a
 
 
 def workload_name(a):
     t = f"_tess{a.tess}_{32 * a.tess * a.tess}tri" if a.tess else ""
-    return f"cornell_box{t}_{a.res}x{a.res}_{a.spp}spp_b{a.bounces}"
+    return f"cornell_box{t}_{a.width}x{a.height}_{a.spp}spp_b{a.bounces}"
 
 
 # ------------------------------------------------------------------ CPU baseline (oracle port, bounded sample)
@@ -63,10 +67,10 @@ def cpu_sample(a, seconds):
         flat = synth.tessellate(ptb.Scene(a.scene or ptb.CORNELL_SDL), a.tess).flatten()
     else:
         flat = scene_port.load_scene(a.scene or ptb.CORNELL_SDL)
-    orc = oracle.Oracle(flat, a.res, a.res)
+    orc = oracle.Oracle(flat, a.width, a.height)
     side = 64 if not a.tess else 4
-    lo = (a.res - side) // 2
-    px = np.array([ix * a.res + iy for ix in range(lo, lo + side) for iy in range(lo, lo + side)], np.int64)
+    lox, loy = (a.width - side) // 2, (a.height - side) // 2
+    px = np.array([ix * a.height + iy for ix in range(lox, lox + side) for iy in range(loy, loy + side)], np.int64)
     t = time.perf_counter()
     orc.trace(1, a.bounces, a.seed, pixels=px, details=False)
     dt = time.perf_counter() - t
@@ -76,7 +80,7 @@ def cpu_sample(a, seconds):
     dt = time.perf_counter() - t
     n = len(px) * spp
     return {"value": n / dt / 1e6, "unit": "Msamples/s", "cores": oracle.num_threads(), "kind": "port",
-            "sample": f"{side}x{side}-pixel centre crop of the {a.res}x{a.res} frame x {spp} spp, b={a.bounces}, "
+            "sample": f"{side}x{side}-pixel centre crop of the {a.width}x{a.height} frame x {spp} spp, b={a.bounces}, "
                       f"FP64 C restatement of the reference (OpenMP), {dt:.1f} s",
             "mrays_per_s": (out["closest_rays"] + out["shadow_rays"]) / dt / 1e6, "seconds": dt, "samples": n}
 
@@ -157,7 +161,7 @@ def run_ours(a):
     if a.tess:
         from pathtracerpython_b200 import synth
         scene = synth.tessellate(scene, a.tess)
-    W = H = a.res
+    W, H = a.width, a.height
     r = ptb.Renderer(scene, device=local)
     px, _ = r.pixels(W, H, rank, world, H)                    # column-interleaved tiles
     full = torch.zeros((W * H, 4), dtype=torch.float32, device=dev)
