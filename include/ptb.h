@@ -72,7 +72,11 @@ enum {
     PTB_FLAG_SEPARATE_KERNELS = 2,  /* A/B and test switch: one primary ray per SAMPLE (default: once per pixel, they are
                                        identical, main.py:191) and, for small scenes, the separate shade / shadow /
                                        closest-hit kernels instead of the fused per-bounce kernel */
-    PTB_FLAG_COUNT_NODES = 4        /* instrumented run: count LBVH nodes visited / triangles tested */
+    PTB_FLAG_COUNT_NODES = 4,       /* instrumented run: count LBVH nodes visited / triangles tested */
+    PTB_FLAG_PHYSICAL = 8,          /* physical mode (not in the reference): ray queries (t > 0), two-sided
+                                       normals with a true tangent frame, kd / ks / kt as diffuse / Phong / refractive lobes,
+                                       area-uniform NEE with the geometry term, RGB throughput, Russian roulette */
+    PTB_FLAG_NO_ROULETTE = 16       /* physical mode: fixed depth, no Russian roulette (unbiasedness check) */
 };
 
 typedef struct {
@@ -125,6 +129,7 @@ int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, dou
 /* replaces make_screen_pts + make_rays + one round of intersect_objects over all primary rays
  * (utils.py:55-69, main.py:191, 199-204, 83-122).  d_tri[i]: global triangle id or -1; d_t[i]:
  * signed ray parameter of the hit (unit direction) or 0.  n outputs = size of the pixel set. */
+size_t ptb_trace_primary_workspace(int64_t n_pixels, int32_t precision);   /* bytes ptb_trace_primary needs */
 int ptb_trace_primary(const ptb_scene *scene, const ptb_pixels *px, int32_t precision, int32_t flags,
                       int32_t *d_tri, float *d_t, void *d_workspace, size_t workspace_bytes, void *stream);
 

@@ -6,10 +6,15 @@
 ignored: they open windows (PIL viewer, OpenGL debug viewer) and there is no display or graphics stack
 on this box.  Extras (off by default, the reference ignores these scene keywords, A-Q19):
 `--use-npaths` takes -r from the scene's `npaths`, `--seed` overrides the scene's `seed` as Philox key,
-`--size W H` overrides `size`."""
+`--size W H` overrides `size`, `--physical` selects physical mode (ray queries, true tangent frame, RGB
+throughput, refraction for `kt`, Russian roulette; include/ptb.h PTB_FLAG_PHYSICAL), `--aov F.npz` dumps the
+primary-hit buffers (triangle id, ray parameter, hit point, normal, object id) that the reference's debug
+viewer draws (plot.py:28-42, 98-105) - as arrays, there is no window."""
 import argparse
 
-from . import render
+import numpy as np
+
+from . import FLAG_PHYSICAL, Renderer, render
 from .scene import Scene
 
 
@@ -24,13 +29,19 @@ def main(argv=None):
     ap.add_argument("--use-npaths", action="store_true")
     ap.add_argument("--seed", type=int, default=None)
     ap.add_argument("--size", type=int, nargs=2, default=None)
+    ap.add_argument("--physical", action="store_true")
+    ap.add_argument("--aov", default=None, help="write primary-hit AOVs to this .npz")
     a = ap.parse_args(argv)
     scene = Scene(a.scene, quiet=False)
     print(f"Number of objects: {len(scene.objects)}")
     print(f"Number of triangles: {sum(len(o['geometry'].triangles) for o in scene.objects)}")
     n_rays = scene.npaths if (a.use_npaths and scene.npaths) else a.n_rays
     w, h = a.size if a.size else (None, None)
-    im = render(scene, n_rays, a.n_bounces, seed=a.seed, width=w, height=h)
+    if a.aov:
+        r = Renderer(scene)
+        np.savez_compressed(a.aov, **r.aovs(w, h))
+        r.close()
+    im = render(scene, n_rays, a.n_bounces, seed=a.seed, width=w, height=h, flags=FLAG_PHYSICAL if a.physical else 0)
     if a.out is not None:
         im.save(a.out)
     return 0

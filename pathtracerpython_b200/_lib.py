@@ -8,12 +8,12 @@ LIB_PATH = os.path.join(_HERE, "libptb.so")
 
 PREC_FP32, PREC_FP64 = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
-FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES = 1, 2, 4
+FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES, FLAG_PHYSICAL, FLAG_NO_ROULETTE = 1, 2, 4, 8, 16
 
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
-           "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak"]
+           "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace"]
 
 
 class PtbError(RuntimeError):
@@ -63,6 +63,8 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.ptb_last_error.restype = C.c_char_p
         L.ptb_trace_paths_workspace.restype = C.c_size_t
+        L.ptb_trace_primary_workspace.restype = C.c_size_t
+        L.ptb_trace_primary_workspace.argtypes = [C.c_int64, C.c_int32]
         L.ptb_pixel_count.restype = C.c_int64
         L.ptb_scene_create.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.POINTER(C.c_void_p)]
         L.ptb_scene_destroy.argtypes = [C.c_void_p]

@@ -13,6 +13,7 @@
 #include "ptb_bvh_kernels.cuh"
 #include "ptb_bvh_dyn.cuh"
 #include "ptb_fused.cuh"
+#include "ptb_phys.cuh"
 
 namespace ptb {
 

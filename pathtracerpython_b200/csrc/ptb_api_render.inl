@@ -93,7 +93,7 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
     }
     const int grid = grid_for(upper, PTB_TRACE_THREADS, 8);
     if (!track && s->use_planes)
-        k_closest_planes32<<<grid, PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(s->d, s->planes, q.qo[in], q.qd[in], d_count, hit_t, hit_tri);
+        k_closest_planes32<false><<<grid, PTB_TRACE_THREADS, plane_smem_bytes(s->planes.n_planes), st>>>(s->d, s->planes, q.qo[in], q.qd[in], d_count, hit_t, hit_tri);
     else if (track)
         k_closest_brute32<true><<<grid, PTB_TRACE_THREADS, smem_tris(s->d.n_tri), st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
     else
@@ -114,6 +114,11 @@ static int launch_closest64(const ptb_scene *s, const double4 *qo, const double4
 }
 
 }  // namespace ptb
+
+extern "C" size_t ptb_trace_primary_workspace(int64_t n_pixels, int32_t precision) {
+    const size_t n = (size_t)std::max<int64_t>(n_pixels, 1);
+    return precision == PTB_PREC_FP64 ? queue_bytes<double>(n, 1) : queue_bytes<float>(n, 1);
+}
 
 extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32_t precision, int32_t flags,
                                  int32_t *d_tri, float *d_t, void *d_ws, size_t ws_bytes, void *stream) {
@@ -319,6 +324,82 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
     return PTB_OK;
 }
 
+// one batch, physical mode (ptb_phys.cuh): same wavefront, ray semantics, RGB throughput, Russian roulette
+static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queues<float> &q, BatchInfo bi, float4 *accum,
+                            cudaStream_t st) {
+    const size_t N = (size_t)bi.npix * bi.S;
+    const DScene &d = s->d;
+    const bool lbvh = d.accel == PTB_ACCEL_LBVH;
+    const int no_rr = (p->flags & PTB_FLAG_NO_ROULETTE) ? 1 : 0;
+    { ProfScope ps_(PK_GEN, st);
+    k_gen_pixels<<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, 1, q.count, q.unc_count, p->bounces + 2);
+    }
+    PTB_LAUNCHED();
+    PTB_CUDA(cudaMemsetAsync(q.count_sh, 0, (size_t)(p->bounces + 2) * sizeof(unsigned), st));
+    const bool sorting = lbvh && s->sort_rays;
+    const unsigned *order = nullptr;
+    const size_t smem = plane_smem_bytes(s->planes.n_planes);
+    for (int b = 0; b < p->bounces; ++b) {
+        const int in = b & 1, out = in ^ 1;
+        bi.bounce = b;
+        const size_t upper = b == 0 ? (size_t)bi.npix : N;
+        { ProfScope ps_(PK_CLOSEST, st);
+        if (lbvh) {
+            unsigned *work = q.work + (g_work_slot++ & 31);
+            PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
+            k_closest_bvh32_dyn<false, false, true><<<grid_for(upper, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
+                d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
+        } else {
+            k_closest_planes32<true><<<grid_for(upper, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem, st>>>(
+                d, s->planes, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri);
+        }
+        }
+        PTB_LAUNCHED();
+        { ProfScope ps_(PK_SHADE, st);
+        k_shade_phys32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
+            d, bi, q.qo[in], q.qd[in], q.kgb[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.count_sh + b, q.qo[out], q.qd[out],
+            q.kgb[out], q.sh_p, q.sh_d, q.sh_aux, q.sh_w, q.sh_res, q.L, q.cap, sorting ? q.sort.keys[0] : nullptr, b == 0 ? 1 : 0,
+            b == p->bounces - 1 ? 1 : 0, no_rr);
+        }
+        PTB_LAUNCHED();
+        if (sorting && b + 1 < p->bounces) {
+            ProfScope ps_(PK_SORT, st);
+            const SortBufs &sb = q.sort;
+            const int blocks = (sb.tiles_max + PS_WARPS - 1) / PS_WARPS;
+            int cur = 0;
+            for (int pass = 0; pass < 3; ++pass) {
+                k_ps_hist<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist);
+                k_ps_rowscan<<<256, 1024, 0, st>>>(sb.ghist, sb.tiles_max, sb.totals);
+                k_ps_scatter<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass,
+                                                              sb.tiles_max, sb.ghist, sb.totals, sb.keys[cur ^ 1], sb.vals[cur ^ 1]);
+                g_launches += 3;
+                cur ^= 1;
+            }
+            order = sb.vals[1];
+            PTB_LAUNCHED(); --g_launches;
+        }
+        { ProfScope ps_(PK_SHADOW, st);
+        if (lbvh) {
+            unsigned *work = q.work + (g_work_slot++ & 31);
+            PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
+            k_shadow_bvh32_dyn<false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
+                d, q.sh_p, q.sh_d, q.count_sh + b, q.sh_res, q.cap, work, nullptr);
+        } else {
+            k_shadow_planes_phys32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem, st>>>(
+                s->planes, q.sh_p, q.sh_d, q.count_sh + b, q.sh_res, q.cap);
+        }
+        PTB_LAUNCHED();
+        k_nee_finish_phys32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_aux, q.sh_w, q.sh_res, q.count_sh + b, q.L, q.cap);
+        }
+        PTB_LAUNCHED();
+    }
+    { ProfScope ps_(PK_REDUCE, st);
+    k_reduce<float><<<grid_for((size_t)bi.npix, 256, 8), 256, 0, st>>>(q.L, accum, bi.npix, bi.S);
+    }
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
 // one batch, FP64 validation path (reference operation order)
 static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<double> &q, BatchInfo bi, RecPtrs rec,
                        float4 *accum, cudaStream_t st) {
@@ -389,6 +470,10 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         return PTB_ERR_NOMEM;
     }
     RecPtrs rec = make_rec(records, npix, n_samples, p->bounces);
+    if (p->flags & PTB_FLAG_PHYSICAL) {
+        if (f64 || rec.any) { set_error("physical mode runs in FP32 and has no reference records"); return PTB_ERR_UNSUPPORTED; }
+        if (s->d.accel == PTB_ACCEL_BRUTE && !s->use_planes) { set_error("physical mode needs the plane-grouped records"); return PTB_ERR_UNSUPPORTED; }
+    }
     g_count_nodes = (p->flags & PTB_FLAG_COUNT_NODES) != 0;
     if (rec.any) {
         const size_t n = (size_t)npix * n_samples * p->bounces;
@@ -406,7 +491,8 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         bi.S = std::min(S, p->sample_end - s0);
         bi.s_first = s0;
         rec.s_off = s0 - p->sample_begin;
-        rc = f64 ? run_batch64(s, p, q64, bi, rec, (float4 *)d_accum, st) : run_batch32(s, p, q32, bi, rec, (float4 *)d_accum, st);
+        if (p->flags & PTB_FLAG_PHYSICAL) rc = run_batch_phys32(s, p, q32, bi, (float4 *)d_accum, st);
+        else rc = f64 ? run_batch64(s, p, q64, bi, rec, (float4 *)d_accum, st) : run_batch32(s, p, q32, bi, rec, (float4 *)d_accum, st);
         if (rc) return rc;
     }
     return PTB_OK;

@@ -35,7 +35,8 @@ __device__ __forceinline__ unsigned claim_work(bool want, unsigned *work, unsign
 }
 
 // ---------------------------------------------------------------- closest hit
-template <bool TRACK, bool COUNT>
+// PHYS (physical mode): ray semantics, only t > tmin counts; boxes behind the origin are skipped.
+template <bool TRACK, bool COUNT, bool PHYS = false>
 __global__ void __launch_bounds__(PTB_BVH_THREADS)
 k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__restrict__ qd, const unsigned *__restrict__ d_count,
                     float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
@@ -73,9 +74,10 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
             slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
             const float lim = TRACK ? h.abs_t + uc.best_dt : h.abs_t;
-            const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
+            const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
             bool go0 = (tn0 <= tf0) && (k0 <= lim), go1 = (tn1 <= tf1) && (k1 <= lim);
-            if (!TRACK) {   // a box the line leaves before |t| reaches the self-hit guard holds no acceptable hit (main.py:100)
+            if (PHYS) { go0 = go0 && (tf0 >= PTB_TMIN_SAFE); go1 = go1 && (tf1 >= PTB_TMIN_SAFE); }
+            else if (!TRACK) {   // a box the line leaves before |t| reaches the self-hit guard holds no acceptable hit (main.py:100)
                 go0 = go0 && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
                 go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             }
@@ -94,7 +96,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                     const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
                     const int ref = side ? n.d.w : n.d.z;      // leaf: the min-ref field is the triangle itself
                     const float a = fabsf(t);
-                    const bool ok = hit && (t * t > PTB_ZERO_F);
+                    const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
                     if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
                         if (TRACK) {
                             if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
@@ -133,7 +135,9 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
 
 // ---------------------------------------------------------------- shadow rays: one item per (path, light sample)
 // sh_res[s * cap + j] = occluding object index (lowest one for s == 2), or -1
-template <bool COUNT>
+// PHYS: plain any-hit ray query for every light sample (t in (tmin, distance)); the outcome array holds the
+// sample's FLOAT weight written by the shade kernel and an occluded sample is zeroed (ptb_phys.cuh).
+template <bool COUNT, bool PHYS = false>
 __global__ void __launch_bounds__(PTB_BVH_THREADS)
 k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const unsigned *__restrict__ d_count,
                    int *__restrict__ sh_res, int cap, unsigned *work, const unsigned *__restrict__ order) {
@@ -163,7 +167,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                 o = mk3(pk.x, pk.y, pk.z); d = mk3(dv.x, dv.y, dv.z);
                 d2max = dv.w; lim = sqrtf(dv.w) * 1.000001f;
                 lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
-                want_min = s == 2u;
+                want_min = !PHYS && s == 2u;
                 found = 0x7fffffff; found_obj = -1;
                 sp = 0; node = 0;
             }
@@ -176,12 +180,12 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
             float tn0, tf0, tn1, tf1;
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
             slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
-            const float k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
+            const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
             // subtrees matter only while they can still hold a triangle of an earlier object, and only if the
             // line is still inside them once |t| passes the self-occlusion guard (main.py:47-48)
             const int cut = min(found, sc.n_tri_obj);
-            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut) && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
-            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut) && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
+            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut) && ((PHYS ? tf0 : far_abs(tn0, tf0)) >= PTB_TMIN_SAFE);
+            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut) && ((PHYS ? tf1 : far_abs(tn1, tf1)) >= PTB_TMIN_SAFE);
             const int c0 = n.d.x, c1 = n.d.y;
             bool finished = false;
 #pragma unroll
@@ -195,7 +199,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                     float t, dt; bool edge;
                     const bool hit = tri_test32<false>(q0, q1, q2, 0.f, o, d, 0.f, t, edge, dt);
                     const float t2 = t * t;
-                    if (hit && t2 >= PTB_ZERO_F && t2 < d2max) {
+                    if (hit && t2 >= PTB_ZERO_F && t2 < d2max && (!PHYS || t > 0.f)) {
                         const int ref = side ? n.d.w : n.d.z;
                         if (ref < found) {
                             found_obj = __ldg(sc.tri_obj + ref);
@@ -216,7 +220,8 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                 else finished = true;
             }
             if (finished) {
-                sh_res[out_slot] = found_obj;
+                if (!PHYS) sh_res[out_slot] = found_obj;
+                else if (found_obj >= 0) sh_res[out_slot] = 0;      // 0 == 0.0f: the sample's weight is cancelled
                 item = 0xffffffffu;
             }
             if (!exhausted && __popc(__activemask()) < PTB_DYN_MIN) break;

@@ -13,6 +13,7 @@ namespace ptb {
 
 #define PTB_ZERO_F 1e-5f
 #define PTB_ZERO_D 1e-5
+#define PTB_TMIN_F 3.1622776e-3f   // sqrt(1e-5): |t| threshold equivalent to squared_dist > ZERO
 
 // ---------------------------------------------------------------- FP32
 struct Hit32 {

@@ -50,10 +50,11 @@ __device__ __forceinline__ float bary_min(const float4 q1, const float4 q2, floa
     return fminf(fminf(u, v), 1.0f - u - v);
 }
 
-#define PTB_TMIN_F 3.1622776e-3f   // sqrt(1e-5): |t| threshold equivalent to squared_dist > ZERO
 
 // ---------------------------------------------------------------- closest hit
 // Warp-collective (votes): all 32 lanes must call it together; lanes with live == false never keep a group alive.
+// PHYS (physical mode): a RAY query, only hits in front of the origin count (t > tmin).
+template <bool PHYS = false>
 __device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_planes, const float4 a, const float4 b, bool live,
                                                  float &best_t, int &best_ref) {
     float best_a = live ? 3.0e38f : 0.f;
@@ -65,7 +66,7 @@ __device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_p
         const float on = nd.w - fmaf(nd.z, a.z, fmaf(nd.y, a.y, nd.x * a.x));
         const float t = on * rcp_approx(dn);
         const float at = fabsf(t);
-        const bool ok = (fabsf(dn) > PTB_ZERO_F) && (at > PTB_TMIN_F) && (at < best_a);
+        const bool ok = (fabsf(dn) > PTB_ZERO_F) && ((PHYS ? t : at) > PTB_TMIN_F) && (at < best_a);
         if (!__any_sync(0xffffffffu, ok)) continue;
         const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
         if (planes[g].kind) {                   // warp-uniform
@@ -83,6 +84,7 @@ __device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_p
     }
 }
 
+template <bool PHYS>
 __global__ void __launch_bounds__(PTB_TRACE_THREADS)
 k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, const float4 *__restrict__ qd,
                    const unsigned *__restrict__ d_count, float *__restrict__ hit_t, int *__restrict__ hit_tri) {
@@ -96,7 +98,7 @@ k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, cons
         const bool live = i < count;
         const float4 a = live ? qo[i] : make_float4(0, 0, 0, 0), b = live ? qd[i] : make_float4(1, 0, 0, 0);
         float best_t; int best_ref;
-        closest_planes32(planes, ps.n_planes, a, b, live, best_t, best_ref);
+        closest_planes32<PHYS>(planes, ps.n_planes, a, b, live, best_t, best_ref);
         if (live) {
             hit_t[i] = best_t;
             hit_tri[i] = best_ref;
@@ -109,6 +111,7 @@ k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, cons
 // Warp-collective.  pk.xyz = shaded point, d0..d2 = unit directions (w = squared distance to the light
 // sample).  occ0 / occ1: sample occluded; leak_ref: lowest reference index among the occluders of sample
 // 2, 0x7fffffff if it is unoccluded (-1 for dead lanes).
+template <bool PHYS = false>
 __device__ __forceinline__ void shadow_planes32(const PlaneRec *planes, int n_occ, const float4 pk, const float4 d0, const float4 d1,
                                                 const float4 d2, bool live, bool &occ0, bool &occ1, int &leak_ref) {
     occ0 = !live; occ1 = !live;            // dead lanes never keep a group alive
@@ -122,9 +125,10 @@ __device__ __forceinline__ void shadow_planes32(const PlaneRec *planes, int n_oc
         const float t0 = on * rcp_approx(dn0), t1 = on * rcp_approx(dn1), t2 = on * rcp_approx(dn2);
         const float s0 = t0 * t0, s1 = t1 * t1, s2 = t2 * t2;
         // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
-        const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w);
-        const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w);
-        const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
+        // PHYS: ray semantics, occluders behind the shaded point do not count
+        const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w) && (!PHYS || t0 > 0.f);
+        const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w) && (!PHYS || t1 > 0.f);
+        const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w) && (!PHYS || t2 > 0.f);
         if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
         const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
         const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);

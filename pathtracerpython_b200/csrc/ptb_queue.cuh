@@ -46,6 +46,9 @@ template <typename T> struct Queues {
     unsigned *count;       // [bounces + 2] live-path count entering each bounce
     unsigned *unc_count;   // number of uncertain primary rays
     int *unc_list;         // their queue positions
+    float2 *kgb[2];        // physical mode: green / blue throughput of the ray queues (red rides in qo.w)
+    float2 *sh_w;          // physical mode: [4][cap] per light sample (diffuse, specular) weights, [3] = throughput g, b
+    unsigned *count_sh;    // physical mode: [bounces + 2] shadow work items per bounce (own compaction)
     SortBufs sort;         // per-bounce re-ordering of the live slots (LBVH scenes, ptb_sort.cuh)
     int cap;               // paths per batch
 };
@@ -55,8 +58,9 @@ template <typename T> inline size_t queue_bytes(size_t cap, int bounces) {
     size_t per = 4 * v + sizeof(T) + sizeof(int) + v + 3 * v + sizeof(int2) + v + sizeof(int) + 3 * sizeof(int);
     per += 4 * sizeof(unsigned);                                    // sort keys / values, ping-pong
     per += sizeof(T) + sizeof(int);                                 // second hit record set
+    per += 6 * sizeof(float2);                                      // physical mode: kgb x 2, sh_w x 4
     const size_t tiles = (cap + PS_TILE - 1) / PS_TILE;
-    return per * cap + 256 * 32 + tiles * 256 * sizeof(unsigned) + 2048 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
+    return per * cap + 256 * 40 + (size_t)(bounces + 8) * sizeof(unsigned) + tiles * 256 * sizeof(unsigned) + 2048 + (size_t)(bounces + 8) * sizeof(unsigned) + 1024;
 }
 
 // carve a workspace into queues; returns bytes used (0 if it does not fit)
@@ -72,6 +76,9 @@ template <typename T> inline size_t queue_carve(void *ws, size_t bytes, size_t c
     q.L = (v4 *)take(cap * sizeof(v4));
     q.hit_t = (T *)take(cap * sizeof(T));
     q.hit_tri = (int *)take(cap * sizeof(int));
+    q.kgb[0] = (float2 *)take(cap * sizeof(float2)); q.kgb[1] = (float2 *)take(cap * sizeof(float2));
+    q.sh_w = (float2 *)take(4 * cap * sizeof(float2));
+    q.count_sh = (unsigned *)take((size_t)(bounces + 4) * sizeof(unsigned));
     q.hit_t2 = (T *)take(cap * sizeof(T));
     q.hit_tri2 = (int *)take(cap * sizeof(int));
     q.sh_aux = (int2 *)take(cap * sizeof(int2));

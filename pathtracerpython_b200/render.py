@@ -102,11 +102,28 @@ class Renderer:
         n = self.pixel_count(px)
         tri = torch.empty(n, dtype=torch.int32, device=self.device)
         t = torch.empty(n, dtype=torch.float32, device=self.device)
-        ws = self.workspace(max(1 << 20, n * 400))
+        ws = self.workspace(int(_lib.lib().ptb_trace_primary_workspace(n, precision)))
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().ptb_trace_primary(self._handle, C.byref(px), precision, flags, tri.data_ptr(), t.data_ptr(),
                                                     ws.data_ptr(), ws.numel(), self._stream()), "ptb_trace_primary")
         return tri, t
+
+    def aovs(self, width=None, height=None):
+        """Primary-hit buffers as numpy arrays in ray-index order (r = ix * H + iy): the data behind the
+        reference's debug views (`--show-inter`, `--show-normals`; plot.py:28-42, 98-105), headless."""
+        W, H = int(width or self.width), int(height or self.height)
+        tri, t = self.trace_primary(W, H)
+        tri, t = tri.cpu().numpy(), t.cpu().numpy().astype(np.float64)
+        f = self.flat
+        eye, (x0, y0, x1, y1) = np.asarray(f["eye"], np.float64), [float(v) for v in f["ortho"]]
+        xs, ys = np.linspace(x0, x1, W), np.linspace(y0, y1, H)             # utils.py:64-69
+        d = np.stack([np.repeat(xs, H), np.tile(ys, W), np.zeros(W * H)], 1) - eye
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        hit = tri >= 0
+        safe = np.where(hit, tri, 0)
+        return {"tri": tri, "t": np.where(hit, t, np.nan), "point": np.where(hit[:, None], eye + d * t[:, None], np.nan),
+                "normal": np.where(hit[:, None], np.asarray(f["normals"])[safe], np.nan),
+                "object": np.where(hit, np.asarray(f["tri_obj"])[safe], -1), "width": W, "height": H}
 
     def trace_closest(self, rays, precision=_lib.PREC_FP32):
         """intersect_objects for caller-supplied rays [n, 6] (origin, direction)."""

@@ -232,6 +232,21 @@ def test_render_drop_in(tmp_path):
     assert a.max() == 255 and a.min() == 0
 
 
+def test_aovs_and_cli(tmp_path, flat):
+    from pathtracerpython_b200.__main__ import main
+    out, aov = str(tmp_path / "o.png"), str(tmp_path / "a.npz")
+    assert main([ptb.CORNELL_SDL, "--out", out, "-r", "2", "-b", "2", "--aov", aov, "--show-img"]) == 0
+    assert main([ptb.CORNELL_SDL, "--out", str(tmp_path / "p.png"), "-r", "2", "-b", "3", "--physical", "--size", "24", "24"]) == 0
+    z = np.load(aov)
+    want, d2, _ = oracle.Oracle(flat).primary()
+    assert np.array_equal(z["tri"], want)
+    hit = want >= 0
+    assert np.allclose(np.linalg.norm(z["point"][hit] - np.asarray(flat["eye"]), axis=1) ** 2, d2[hit], rtol=1e-5)
+    assert np.array_equal(z["object"][hit], np.asarray(flat["tri_obj"])[want[hit]])
+    from PIL import Image
+    assert Image.open(out).size == (40, 40)
+
+
 def test_errors_are_loud(rnd):
     with pytest.raises(ptb.PtbError):
         rnd.trace_paths(1, 1, shard=5, n_shards=2)
