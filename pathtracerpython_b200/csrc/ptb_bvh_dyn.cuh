@@ -180,12 +180,18 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
             float tn0, tf0, tn1, tf1;
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
             slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
-            const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
-            // subtrees matter only while they can still hold a triangle of an earlier object, and only if the
-            // line is still inside them once |t| passes the self-occlusion guard (main.py:47-48)
+            // The query range is |t| <= lim (both directions, A-Q1) minus the self-occlusion guard |t| < tmin
+            // (main.py:47-48): the box matters if its interval [tn, tf] meets [-lim, lim] and is not inside (-tmin, tmin);
+            // PHYS keeps only the forward half.  Subtrees also matter only while they can still hold a triangle of an
+            // earlier object than the best occluder.  No nearest-first ordering: the query is any-hit / exhaustive.
             const int cut = min(found, sc.n_tri_obj);
-            bool go0 = (tn0 <= tf0) && (k0 <= lim) && (n.d.z < cut) && ((PHYS ? tf0 : far_abs(tn0, tf0)) >= PTB_TMIN_SAFE);
-            bool go1 = (tn1 <= tf1) && (k1 <= lim) && (n.d.w < cut) && ((PHYS ? tf1 : far_abs(tn1, tf1)) >= PTB_TMIN_SAFE);
+            bool go0 = (tn0 <= tf0) && (tn0 <= lim) && (n.d.z < cut);
+            bool go1 = (tn1 <= tf1) && (tn1 <= lim) && (n.d.w < cut);
+            if (PHYS) { go0 = go0 && (tf0 >= PTB_TMIN_SAFE); go1 = go1 && (tf1 >= PTB_TMIN_SAFE); }
+            else {
+                go0 = go0 && (tf0 >= -lim) && (fmaxf(-tn0, tf0) >= PTB_TMIN_SAFE);
+                go1 = go1 && (tf1 >= -lim) && (fmaxf(-tn1, tf1) >= PTB_TMIN_SAFE);
+            }
             const int c0 = n.d.x, c1 = n.d.y;
             bool finished = false;
 #pragma unroll
@@ -211,11 +217,8 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
             }
             go0 = go0 && c0 >= 0 && (n.d.z < found); go1 = go1 && c1 >= 0 && (n.d.w < found);
             if (!finished) {
-                if (go0 && go1) {
-                    const bool first1 = k1 < k0;
-                    stack[sp++] = first1 ? c0 : c1;
-                    node = first1 ? c1 : c0;
-                } else if (go0 || go1) node = go0 ? c0 : c1;
+                if (go0 && go1) { stack[sp++] = c1; node = c0; }
+                else if (go0 || go1) node = go0 ? c0 : c1;
                 else if (sp > 0) node = stack[--sp];
                 else finished = true;
             }

@@ -34,13 +34,12 @@ __device__ __forceinline__ void slab(const LineBox<double> &r, float lx, float l
     tn = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmin(az, bz));
     tf = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
 }
-// smallest |t| of [tn, tf]
-template <typename T> __device__ __forceinline__ T near_abs(T tn, T tf) {
-    return (tn <= (T)0 && tf >= (T)0) ? (T)0 : (fabs(tn) < fabs(tf) ? fabs(tn) : fabs(tf));
-}
-
+// smallest |t| of [tn, tf] (tn <= tf): tn if the interval is in front, -tf if it is behind, else 0
+__device__ __forceinline__ float near_abs(float tn, float tf) { return fmaxf(fmaxf(tn, -tf), 0.0f); }
+__device__ __forceinline__ double near_abs(double tn, double tf) { return fmax(fmax(tn, -tf), 0.0); }
 // largest |t| of [tn, tf]
-template <typename T> __device__ __forceinline__ T far_abs(T tn, T tf) { return fabs(tn) > fabs(tf) ? fabs(tn) : fabs(tf); }
+__device__ __forceinline__ float far_abs(float tn, float tf) { return fmaxf(-tn, tf); }
+__device__ __forceinline__ double far_abs(double tn, double tf) { return fmax(-tn, tf); }
 // sqrt(1e-5) = 3.1623e-3 is the smallest |t| either query accepts (main.py:47-48, 100); boxes are padded and
 // the FP32 ray parameter carries ~1e-5 of error, so prune only below 3.0e-3
 #define PTB_TMIN_SAFE 3.0e-3f
