@@ -107,6 +107,15 @@ template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, c
     return PTB_OK;
 }
 
+template <typename T> static int upload_raw(ptb_scene *s, const T *src, size_t count, const T **out, cudaStream_t st) {
+    void *p = nullptr;
+    PTB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    s->allocs.push_back(p);
+    if (count) PTB_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+    *out = (const T *)p;
+    return PTB_OK;
+}
+
 static inline float bits_f(int v) { float f; memcpy(&f, &v, 4); return f; }
 static inline void cross_h(const double *a, const double *b, double *c) {
     c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
@@ -211,10 +220,10 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
     DScene &d = s->d;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    const int n_tiles = (n + PS_TILE - 1) / PS_TILE;
     Aabb *tri_box = nullptr, *node_box = nullptr; float4 *centroid = nullptr; unsigned *scene_box = nullptr, *keys[2] = {nullptr, nullptr};
     int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
-    unsigned *ghist = nullptr, *flags = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
+    unsigned *ghist = nullptr, *flags = nullptr, *totals = nullptr, *d_n = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
     std::vector<void *> tmp;
     auto alloc = [&](void **p, size_t bytes, bool keep) -> int {
         PTB_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));
@@ -228,11 +237,14 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
         (rc = alloc((void **)&vals[0], 4 * (size_t)n, false)) || (rc = alloc((void **)&vals[1], 4 * (size_t)n, true)) ||
         (rc = alloc((void **)&parent_inner, 4 * (size_t)n, false)) || (rc = alloc((void **)&parent_leaf, 4 * (size_t)n, false)) ||
         (rc = alloc((void **)&node_minref, 4 * (size_t)n, false)) || (rc = alloc((void **)&child, sizeof(int2) * n, false)) ||
-        (rc = alloc((void **)&ghist, 4 * (size_t)256 * n_tiles, false)) || (rc = alloc((void **)&flags, 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&ghist, 4 * (size_t)256 * n_tiles, false)) || (rc = alloc((void **)&totals, 4 * 256, false)) ||
+        (rc = alloc((void **)&d_n, 16, false)) || (rc = alloc((void **)&flags, 4 * (size_t)n, false)) ||
         (rc = alloc((void **)&nodes, sizeof(BvhNode) * (size_t)n, true)) || (rc = alloc((void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true))) {
         for (void *p : tmp) cudaFree(p);
         return rc;
     }
+    const unsigned h_n = (unsigned)n;
+    cudaMemcpyAsync(d_n, &h_n, sizeof(unsigned), cudaMemcpyHostToDevice, st);
     cudaEventRecord(e0, st);
     {
         ProfScope ps_(PK_BUILD, st);
@@ -241,13 +253,15 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
         k_tri_bounds<<<g, 256, 0, st>>>(d.verts64, n, tri_box, centroid, scene_box);
         k_morton<<<g, 256, 0, st>>>(centroid, n, scene_box, keys[0], vals[0]);
         g_launches += 3;
-        // 4 passes x 8 bits; after an even number of passes the result is back in buffer 0 -> copy into the kept buffer
+        // 4 passes x 8 bits of the device-count radix sort (ptb_sort.cuh: per-digit row scans, no single-block
+        // scan over all tiles); after an even number of passes the result is back in buffer 0
         int cur = 0;
-        const int rs_blocks = (n_tiles + RS_WARPS - 1) / RS_WARPS;
+        const int rs_blocks = (n_tiles + PS_WARPS - 1) / PS_WARPS;
         for (int pass = 0; pass < 4; ++pass) {
-            k_rs_hist<<<rs_blocks, RS_WARPS * 32, 0, st>>>(keys[cur], n, 8 * pass, n_tiles, ghist);
-            k_rs_scan<<<1, 1024, 0, st>>>(ghist, (size_t)256 * n_tiles);
-            k_rs_scatter<<<rs_blocks, RS_WARPS * 32, 0, st>>>(keys[cur], vals[cur], n, 8 * pass, n_tiles, ghist, keys[cur ^ 1], vals[cur ^ 1]);
+            k_ps_hist<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], d_n, 8 * pass, n_tiles, ghist);
+            k_ps_rowscan<<<256, 1024, 0, st>>>(ghist, n_tiles, totals);
+            k_ps_scatter<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], (const unsigned *)vals[cur], d_n, 8 * pass, n_tiles, ghist, totals,
+                                                             keys[cur ^ 1], (unsigned *)vals[cur ^ 1]);
             g_launches += 3;
             cur ^= 1;
         }
@@ -298,22 +312,67 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     memset(&s->d, 0, sizeof(DScene));
     cudaGetDevice(&s->device);
     const int n = desc->n_tri, no = desc->n_obj;
-    double scale = 1.0;
-    for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
+    // Large scenes (LBVH): the FP64 arrays are uploaded straight from the caller's buffers and the FP32 records,
+    // shading normals, scene extent and scale are computed on the device (ptb_bvh_build.cuh); small scenes keep
+    // the host loop because the plane grouping below needs the records on the host.
+    const bool dev_records = accel == PTB_ACCEL_LBVH;
+    DScene &d = s->d;
+    int rc = PTB_OK;
+    double scale = 1.0, blo[3] = {1e300, 1e300, 1e300}, bhi[3] = {-1e300, -1e300, -1e300};
+    std::vector<TriRec> tri;
+    std::vector<float4> sn;
+    std::vector<int> ids;
+    if (dev_records) {
+        if ((rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st)) ||
+            (rc = upload_raw(s, desc->tri_obj, (size_t)n, &d.tri_obj, st))) { ptb_scene_destroy(s); return rc; }
+        const int blocks = grid_for((size_t)n * 3, 256, 4);
+        double *d_ext = nullptr;
+        std::vector<double> h_ext((size_t)blocks * 8);
+        if (cudaMalloc(&d_ext, h_ext.size() * sizeof(double)) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        k_scene_extent<<<blocks, 256, 0, st>>>(d.verts64, (size_t)n * 3, d.tri_obj, n, no, d_ext);
+        ++g_launches;
+        cudaMemcpyAsync(h_ext.data(), d_ext, h_ext.size() * sizeof(double), cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFree(d_ext);
+        if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("scene extent: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
+        bool bad_obj = false;
+        for (int b = 0; b < blocks; ++b) {
+            const double *x = h_ext.data() + 8 * (size_t)b;
+            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], x[k]); bhi[k] = std::max(bhi[k], x[3 + k]); }
+            scale = std::max(scale, x[6]);
+            bad_obj = bad_obj || x[7] != 0.0;
+        }
+        if (bad_obj) { ptb_scene_destroy(s); set_error("tri_obj out of range"); return PTB_ERR_ARG; }
+    } else {
+        for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
+        for (size_t i = 0; i < (size_t)n * 3; ++i)
+            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], desc->verts[3 * i + k]); bhi[k] = std::max(bhi[k], desc->verts[3 * i + k]); }
+    }
     for (int i = 0; i < 3; ++i) scale = std::max(scale, fabs(desc->eye[i]));
     s->dt_scale = (float)(32.0 * 5.9604644775390625e-08 * scale);
+    for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)blo[k]; d.bb_inv[k] = (float)(256.0 / std::max(bhi[k] - blo[k], 1e-30)); }
 
-    std::vector<TriRec> tri(n);
-    std::vector<float4> sn(n);
-    std::vector<int> ids(n), tobj(desc->tri_obj, desc->tri_obj + n);
-    for (int i = 0; i < n; ++i) {
-        if (tobj[i] < 0 || tobj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
-        tri[i] = make_trirec(desc->verts + 9 * (size_t)i, tobj[i], scale);
-        tri[i].q3.w = bits_f(i);                     // reference index travels with the record (LBVH leaf order)
-        const double *nn = desc->normals + 3 * (size_t)i;
-        sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(tobj[i]));
-        ids[i] = i;
+    if (dev_records) {
+        TriRec *d_tri = nullptr; float4 *d_sn = nullptr;
+        if (cudaMalloc((void **)&d_tri, sizeof(TriRec) * (size_t)n) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(d_tri);
+        if (cudaMalloc((void **)&d_sn, sizeof(float4) * (size_t)n) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(d_sn);
+        k_make_records<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, d.normals64, d.tri_obj, n, scale, d_tri, d_sn);
+        ++g_launches;
+        d.tri = d_tri; d.tri_sn = d_sn; d.tri_id = nullptr;
+    } else {
+        tri.resize(n); sn.resize(n); ids.resize(n);
+        for (int i = 0; i < n; ++i) {
+            if (desc->tri_obj[i] < 0 || desc->tri_obj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
+            tri[i] = make_trirec(desc->verts + 9 * (size_t)i, desc->tri_obj[i], scale);
+            tri[i].q3.w = bits_f(i);                     // reference index travels with the record (LBVH leaf order)
+            const double *nn = desc->normals + 3 * (size_t)i;
+            sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(desc->tri_obj[i]));
+            ids[i] = i;
+        }
     }
+    const int32_t *tobj = desc->tri_obj;
     std::vector<double> mat64((size_t)(no + 1) * 8, 0.0);
     std::copy(desc->mat, desc->mat + (size_t)no * 8, mat64.begin());
     std::vector<float> mat32(mat64.begin(), mat64.end());
@@ -350,7 +409,6 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         lobe_thr[k] = (int)first_m([&](unsigned m) { return !(0.0 + ((kd + ks) - 0.0) * ((double)m * 5.9604644775390625e-08) <= kd); });
         if (ne >= 0.0 && ne <= 64.0 && ne == floor(ne)) pow_int[k] = (int)ne;
     }
-    std::vector<double> verts(desc->verts, desc->verts + (size_t)n * 9), normals(desc->normals, desc->normals + (size_t)n * 3);
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<int> obj_first(no + 2, n);
     for (int i = n - 1; i >= 0; --i) obj_first[tobj[i]] = i;
@@ -358,12 +416,16 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     std::vector<PlaneRec> planes; int n_occ = 0;
     if (accel == PTB_ACCEL_BRUTE) build_plane_groups(desc, tri, planes, n_occ);
 
-    DScene &d = s->d;
-    int rc = PTB_OK;
-    if ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
-        (rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) || (rc = upload(s, verts, &d.verts64, st)) ||
-        (rc = upload(s, normals, &d.normals64, st)) || (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
-        (rc = upload(s, tobj, &d.tri_obj, st)) || (rc = upload(s, obj_first, &d.obj_first, st)) ||
+    if (!dev_records &&
+        ((rc = upload(s, tri, &d.tri, st)) || (rc = upload(s, ids, &d.tri_id, st)) || (rc = upload(s, sn, &d.tri_sn, st)) ||
+         (rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st)) ||
+         (rc = upload_raw(s, desc->tri_obj, (size_t)n, &d.tri_obj, st)))) {
+        ptb_scene_destroy(s);
+        return rc;
+    }
+    if ((rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) ||
+        (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
+        (rc = upload(s, obj_first, &d.obj_first, st)) ||
         (rc = upload(s, light_thr, &d.light_thr, st)) || (rc = upload(s, lobe_thr, &d.obj_lobe_thr, st)) || (rc = upload(s, pow_int, &d.obj_pow_int, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
@@ -381,12 +443,6 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     s->build_ms = 0.0;
     s->n_nodes = 0;
     s->pad = (float)(scale * 3.814697265625e-06);   // 2^-18 * scene scale
-    {   // scene box of the per-bounce sort keys (ptb_sort.cuh)
-        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-        for (size_t i = 0; i < (size_t)n * 3; ++i)
-            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], desc->verts[3 * i + k]); hi[k] = std::max(hi[k], desc->verts[3 * i + k]); }
-        for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)lo[k]; d.bb_inv[k] = (float)(256.0 / std::max(hi[k] - lo[k], 1e-30)); }
-    }
     if (accel == PTB_ACCEL_LBVH) {
         const TriRec *ref_order = d.tri;      // the reference-order array stays allocated: source of both gathers
         double ms_all = 0.0, ms_occ = 0.0;

@@ -1,7 +1,7 @@
 // ptb_bvh_build.cuh - GPU LBVH build (north_star (1); no reference counterpart):
 //   1. per-triangle bounds + centroid, scene bounds            (k_tri_bounds)
 //   2. 30-bit Morton codes, 10 bits per axis                   (k_morton)
-//   3. LSD radix sort of (code, triangle) pairs, 8 bits/pass   (k_rs_hist / k_rs_scan / k_rs_scatter)
+//   3. LSD radix sort of (code, triangle) pairs, 8 bits/pass   (ptb_sort.cuh: k_ps_hist / k_ps_rowscan / k_ps_scatter)
 //   4. Karras 2012 binary radix tree over the sorted codes     (k_karras)
 //   5. bottom-up AABB refit, second arrival at a node proceeds (k_refit, atomic flags)
 //   6. pack 64 B nodes holding BOTH children's boxes           (k_pack)
@@ -9,6 +9,7 @@
 // triangle whose reference test would accept.
 #pragma once
 #include "ptb_scene.cuh"
+#include "ptb_sort.cuh"
 
 namespace ptb {
 
@@ -83,73 +84,8 @@ k_morton(const float4 *__restrict__ centroid, int n, const unsigned *__restrict_
     }
 }
 
-// ---------------------------------------------------------------- radix sort (stable LSD, 8 bits per pass)
-// Work is split into warp tiles of RS_TILE consecutive elements; a warp walks its tile 32 elements at a
-// time, so order inside a tile is preserved and no block-level synchronisation is needed.
-#define RS_TILE 2048
-#define RS_WARPS 8
-
-__global__ void __launch_bounds__(RS_WARPS * 32)
-k_rs_hist(const unsigned *__restrict__ keys, int n, int shift, int n_tiles, unsigned *__restrict__ ghist /* [256][n_tiles] */) {
-    __shared__ unsigned s_h[RS_WARPS][256];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * RS_WARPS + warp;
-    for (int b = lane; b < 256; b += 32) s_h[warp][b] = 0;
-    __syncwarp();
-    if (tile < n_tiles) {
-        const int beg = tile * RS_TILE, end = min(n, beg + RS_TILE);
-        for (int i = beg + lane; i < end; i += 32) atomicAdd(&s_h[warp][(keys[i] >> shift) & 255u], 1u);
-        __syncwarp();
-        for (int b = lane; b < 256; b += 32) ghist[(size_t)b * n_tiles + tile] = s_h[warp][b];
-    }
-}
-
-// exclusive scan of ghist (bin-major) in place; single block
-__global__ void __launch_bounds__(1024) k_rs_scan(unsigned *ghist, size_t total) {
-    __shared__ unsigned s_part[1024];
-    const size_t per = (total + 1023) / 1024;
-    const size_t beg = per * threadIdx.x, end = beg + per < total ? beg + per : total;
-    unsigned sum = 0;
-    for (size_t i = beg; i < end; ++i) sum += ghist[i];
-    s_part[threadIdx.x] = sum;
-    __syncthreads();
-    // Hillis-Steele inclusive scan of the 1024 partials
-    for (int o = 1; o < 1024; o <<= 1) {
-        unsigned v = threadIdx.x >= (unsigned)o ? s_part[threadIdx.x - o] : 0u;
-        __syncthreads();
-        s_part[threadIdx.x] += v;
-        __syncthreads();
-    }
-    unsigned run = threadIdx.x ? s_part[threadIdx.x - 1] : 0u;
-    for (size_t i = beg; i < end; ++i) { const unsigned v = ghist[i]; ghist[i] = run; run += v; }
-}
-
-__global__ void __launch_bounds__(RS_WARPS * 32)
-k_rs_scatter(const unsigned *__restrict__ keys, const int *__restrict__ vals, int n, int shift, int n_tiles,
-             const unsigned *__restrict__ ghist, unsigned *__restrict__ keys_out, int *__restrict__ vals_out) {
-    __shared__ unsigned s_off[RS_WARPS][256];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * RS_WARPS + warp;
-    if (tile >= n_tiles) return;
-    for (int b = lane; b < 256; b += 32) s_off[warp][b] = ghist[(size_t)b * n_tiles + tile];
-    __syncwarp();
-    const int beg = tile * RS_TILE, end = min(n, beg + RS_TILE);
-    for (int base = beg; base < end; base += 32) {
-        const int i = base + lane;
-        const bool live = i < end;
-        const unsigned k = live ? keys[i] : 0u;
-        const int v = live ? vals[i] : 0;
-        const unsigned d = live ? ((k >> shift) & 255u) : 256u + lane;   // dead lanes match nobody
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        const unsigned rank = __popc(peers & ((1u << lane) - 1u));
-        unsigned pos = 0;
-        if (live) pos = s_off[warp][d] + rank;
-        __syncwarp();
-        if (live && rank == 0) s_off[warp][d] += __popc(peers);
-        __syncwarp();
-        if (live) { keys_out[pos] = k; vals_out[pos] = v; }
-    }
-}
+// The sort of the (code, triangle) pairs is the stable LSD radix sort of ptb_sort.cuh (8 bits per pass, warp tiles,
+// match_any ranking, per-digit row scans), the same kernels that re-order the live paths between bounces.
 
 // ---------------------------------------------------------------- Karras hierarchy
 // delta(i, j) = common-prefix length of (code_i, i) and (code_j, j); -1 outside [0, n)
@@ -243,6 +179,77 @@ k_pack(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_b
         nd.n0 = c.x < 0 ? sorted_tri[~c.x] : node_minref[c.x];     // lowest reference index below child 0 / 1
         nd.n1 = c.y < 0 ? sorted_tri[~c.y] : node_minref[c.y];
         nodes[i] = nd;
+    }
+}
+
+// Scene extent, max |coordinate| and a tri_obj range check in one pass; every block writes 8 doubles
+// (min xyz, max xyz, max abs, bad-object flag) that the host folds.
+__global__ void __launch_bounds__(256)
+k_scene_extent(const double *__restrict__ verts, size_t n_pts, const int *__restrict__ tri_obj, int n_tri, int n_obj, double *__restrict__ out) {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, mx = 0.0, bad = 0.0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_pts; i += (size_t)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double v = verts[3 * i + k];
+            lo[k] = fmin(lo[k], v); hi[k] = fmax(hi[k], v); mx = fmax(mx, fabs(v));
+        }
+        if (i < (size_t)n_tri && (tri_obj[i] < 0 || tri_obj[i] > n_obj)) bad = 1.0;
+    }
+    __shared__ double s_red[8][8];
+    double v[8] = {lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], mx, bad};
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        for (int o = 16; o > 0; o >>= 1) {
+            const double w = __shfl_xor_sync(0xffffffffu, v[k], o);
+            v[k] = k < 3 ? fmin(v[k], w) : fmax(v[k], w);
+        }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 8; ++k) s_red[threadIdx.x >> 5][k] = v[k];
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        double r = s_red[0][threadIdx.x];
+        for (int w = 1; w < 8; ++w) r = threadIdx.x < 3 ? fmin(r, s_red[w][threadIdx.x]) : fmax(r, s_red[w][threadIdx.x]);
+        out[8 * (size_t)blockIdx.x + threadIdx.x] = r;
+    }
+}
+
+// FP32 traversal records + shading normals from the uploaded FP64 vertices (large scenes: no host loop).
+// Same operations in the same order as the host's make_trirec (ptb_api.cu), one IEEE rounding each, so a
+// triangle gets the same record whichever side builds it.
+__device__ __forceinline__ double hdot(const double *a, const double *b) {   // host dot_h: (a0 b0 + a1 b1) + a2 b2
+    return xadd(xadd(xmul(a[0], b[0]), xmul(a[1], b[1])), xmul(a[2], b[2]));
+}
+__device__ __forceinline__ void hcross(const double *a, const double *b, double *c) {
+    c[0] = xsub(xmul(a[1], b[2]), xmul(a[2], b[1])); c[1] = xsub(xmul(a[2], b[0]), xmul(a[0], b[2])); c[2] = xsub(xmul(a[0], b[1]), xmul(a[1], b[0]));
+}
+__global__ void __launch_bounds__(256)
+k_make_records(const double *__restrict__ verts, const double *__restrict__ normals, const int *__restrict__ tri_obj, int n, double scale,
+               TriRec *__restrict__ tri, float4 *__restrict__ tri_sn) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double *A = verts + 9 * (size_t)i, *B = A + 3, *C = A + 6;
+        double ab[3], cb[3], nn[3], e1[3], e2[3], N[3], mu[3], mv[3], mw[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { ab[k] = xsub(A[k], B[k]); cb[k] = xsub(C[k], B[k]); e1[k] = xsub(B[k], A[k]); e2[k] = xsub(C[k], A[k]); }
+        hcross(ab, cb, nn);
+        const double nl = xsqrt(hdot(nn, nn));
+#pragma unroll
+        for (int k = 0; k < 3; ++k) nn[k] = xdiv(nn[k], nl);
+        hcross(e1, e2, N);
+        const double inv = xdiv(1.0, hdot(N, N));
+        hcross(e2, N, mu);
+        hcross(N, e1, mv);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { mu[k] = xmul(mu[k], inv); mv[k] = xmul(mv[k], inv); mw[k] = xadd(mu[k], mv[k]); }
+        const double g = fmax(xsqrt(hdot(mu, mu)), fmax(xsqrt(hdot(mv, mv)), xsqrt(hdot(mw, mw))));
+        const int obj = tri_obj[i];
+        TriRec r;
+        r.q0 = make_float4((float)nn[0], (float)nn[1], (float)nn[2], (float)hdot(nn, A));
+        r.q1 = make_float4((float)mu[0], (float)mu[1], (float)mu[2], (float)(-hdot(A, mu)));
+        r.q2 = make_float4((float)mv[0], (float)mv[1], (float)mv[2], (float)(-hdot(A, mv)));
+        r.q3 = make_float4((float)xmul(xmul(xmul(32.0, 5.9604644775390625e-08), scale), g), 0.f, __int_as_float(obj), __int_as_float(i));
+        tri[i] = r;
+        const double *sn = normals + 3 * (size_t)i;
+        tri_sn[i] = make_float4((float)sn[0], (float)sn[1], (float)sn[2], __int_as_float(obj));
     }
 }
 
