@@ -19,6 +19,10 @@
 namespace ptb {
 
 #define PTB_DYN_MIN 20     // refill when fewer lanes than this are still traversing
+#ifndef PTB_WW_MIN
+#define PTB_WW_MIN 8       // leave the node loop for the triangle tests when fewer lanes than this are still walking
+#endif
+#define PTB_WW_DONE ((int)0x80000000)   // traversal state: nothing left (leaf codes are ~slot > INT_MIN)
 
 // warp-wide claim of new work items for the lanes with want == true; returns the claimed index or
 // 0xffffffff when the pool [0, count) is exhausted.
@@ -73,6 +77,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
             float tn0, tf0, tn1, tf1;
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
             slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
+            const int c0 = n.d.x, c1 = n.d.y, m0 = n.d.z, m1 = n.d.w;
             const float lim = TRACK ? h.abs_t + uc.best_dt : h.abs_t;
             const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
             bool go0 = (tn0 <= tf0) && (k0 <= lim), go1 = (tn1 <= tf1) && (k1 <= lim);
@@ -81,7 +86,6 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 go0 = go0 && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
                 go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             }
-            const int c0 = n.d.x, c1 = n.d.y;
 #pragma unroll
             for (int side = 0; side < 2; ++side) {
                 const bool go = side ? go1 : go0;
@@ -94,7 +98,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                     if (COUNT) nt++;
                     float t, dt = 0.f; bool edge = false;
                     const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
-                    const int ref = side ? n.d.w : n.d.z;      // leaf: the min-ref field is the triangle itself
+                    const int ref = side ? m1 : m0;            // leaf: the min-ref field is the triangle itself
                     const float a = fabsf(t);
                     const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
                     if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
@@ -174,55 +178,50 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
         }
         if (!__any_sync(0xffffffffu, item != 0xffffffffu)) break;
+        // while-while traversal: lanes walk inner nodes together; a lane that reaches a leaf parks on it (leaves travel
+        // through the stack like inner nodes, encoded ~slot) and the triangle tests run when few lanes are still walking,
+        // so the ~80-instruction test block executes with many lanes instead of one or two per node step.
         while (item != 0xffffffffu) {
-            const NodeBoxes n = ld_node(nodes, node);
-            if (COUNT) nn++;
-            float tn0, tf0, tn1, tf1;
-            slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
-            slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
-            // The query range is |t| <= lim (both directions, A-Q1) minus the self-occlusion guard |t| < tmin
-            // (main.py:47-48): the box matters if its interval [tn, tf] meets [-lim, lim] and is not inside (-tmin, tmin);
-            // PHYS keeps only the forward half.  Subtrees also matter only while they can still hold a triangle of an
-            // earlier object than the best occluder.  No nearest-first ordering: the query is any-hit / exhaustive.
-            const int cut = min(found, sc.n_tri_obj);
-            bool go0 = (tn0 <= tf0) && (tn0 <= lim) && (n.d.z < cut);
-            bool go1 = (tn1 <= tf1) && (tn1 <= lim) && (n.d.w < cut);
-            if (PHYS) { go0 = go0 && (tf0 >= PTB_TMIN_SAFE); go1 = go1 && (tf1 >= PTB_TMIN_SAFE); }
-            else {
-                go0 = go0 && (tf0 >= -lim) && (fmaxf(-tn0, tf0) >= PTB_TMIN_SAFE);
-                go1 = go1 && (tf1 >= -lim) && (fmaxf(-tn1, tf1) >= PTB_TMIN_SAFE);
-            }
-            const int c0 = n.d.x, c1 = n.d.y;
-            bool finished = false;
-#pragma unroll
-            for (int side = 0; side < 2; ++side) {
-                const bool go = side ? go1 : go0;
-                const int c = side ? c1 : c0;
-                if (go && c < 0) {
-                    const float4 *tp = reinterpret_cast<const float4 *>(tris + ~c);
-                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-                    if (COUNT) nt++;
-                    float t, dt; bool edge;
-                    const bool hit = tri_test32<false>(q0, q1, q2, 0.f, o, d, 0.f, t, edge, dt);
-                    const float t2 = t * t;
-                    if (hit && t2 >= PTB_ZERO_F && t2 < d2max && (!PHYS || t > 0.f)) {
-                        const int ref = side ? n.d.w : n.d.z;
-                        if (ref < found) {
-                            found_obj = __ldg(sc.tri_obj + ref);
-                            found = __ldg(sc.obj_first + found_obj);    // first triangle of that object
-                        }
-                        if (!want_min || found == 0) finished = true;
-                    }
+            while (node >= 0) {
+                const NodeBoxes n = ld_node(nodes, node);
+                if (COUNT) nn++;
+                float tn0, tf0, tn1, tf1;
+                slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
+                slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
+                const int c0 = n.d.x, c1 = n.d.y, m0 = n.d.z, m1 = n.d.w;
+                const int cut = min(found, sc.n_tri_obj);
+                bool go0 = (tn0 <= tf0) && (tn0 <= lim) && (m0 < cut);
+                bool go1 = (tn1 <= tf1) && (tn1 <= lim) && (m1 < cut);
+                if (PHYS) { go0 = go0 && (tf0 >= PTB_TMIN_SAFE); go1 = go1 && (tf1 >= PTB_TMIN_SAFE); }
+                else {
+                    go0 = go0 && (tf0 >= -lim) && (fmaxf(-tn0, tf0) >= PTB_TMIN_SAFE);
+                    go1 = go1 && (tf1 >= -lim) && (fmaxf(-tn1, tf1) >= PTB_TMIN_SAFE);
                 }
-            }
-            go0 = go0 && c0 >= 0 && (n.d.z < found); go1 = go1 && c1 >= 0 && (n.d.w < found);
-            if (!finished) {
                 if (go0 && go1) { stack[sp++] = c1; node = c0; }
                 else if (go0 || go1) node = go0 ? c0 : c1;
                 else if (sp > 0) node = stack[--sp];
-                else finished = true;
+                else node = PTB_WW_DONE;
+                if (__popc(__activemask()) < PTB_WW_MIN) break;
             }
-            if (finished) {
+            if (node < 0 && node != PTB_WW_DONE) {                   // parked on a leaf: ~slot
+                const float4 *tp = reinterpret_cast<const float4 *>(tris + ~node);
+                const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                const int ref = __float_as_int(__ldg(reinterpret_cast<const float *>(tp + 3) + 3));
+                if (COUNT) nt++;
+                float t, dt; bool edge;
+                const bool hit = tri_test32<false>(q0, q1, q2, 0.f, o, d, 0.f, t, edge, dt);
+                const float t2 = t * t;
+                bool finished = false;
+                if (hit && t2 >= PTB_ZERO_F && t2 < d2max && (!PHYS || t > 0.f)) {
+                    if (ref < found) {
+                        found_obj = __ldg(sc.tri_obj + ref);
+                        found = __ldg(sc.obj_first + found_obj);    // first triangle of that object
+                    }
+                    if (!want_min || found == 0) finished = true;
+                }
+                node = (finished || sp == 0) ? PTB_WW_DONE : stack[--sp];
+            }
+            if (node == PTB_WW_DONE) {
                 if (!PHYS) sh_res[out_slot] = found_obj;
                 else if (found_obj >= 0) sh_res[out_slot] = 0;      // 0 == 0.0f: the sample's weight is cancelled
                 item = 0xffffffffu;

@@ -80,8 +80,10 @@ class Renderer:
         px.shard, px.n_shards, px.tile = int(shard), int(n_shards), int(tile)
         keep = None
         if pixel_list is not None:
-            keep = self.torch.as_tensor(np.asarray(pixel_list, np.int32), device=self.device)
-            px.n_pixels = keep.numel()
+            lst = np.asarray(pixel_list, np.int32).reshape(-1)
+            px.n_pixels = int(lst.size)
+            # an empty list is still a list (NULL would mean "the whole shard"): keep a 1-element buffer behind it
+            keep = self.torch.as_tensor(lst if lst.size else np.zeros(1, np.int32), device=self.device)
             px.d_pixels = keep.data_ptr()
         return px, keep
 

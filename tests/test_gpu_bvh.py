@@ -145,3 +145,68 @@ def test_one_million_triangles_build_and_consistency(cornell):
     acc, _ = r.trace_paths(2, 3, seed=1, width=256, height=256)
     assert bool(np.isfinite(acc.cpu().numpy()).all())
     r.close()
+
+
+# ------------------------------------------------------------------ edge cases
+def _mini_scene(objects, light_tris, size=24):
+    from pathtracerpython_b200.scene import Obj, Scene
+    s = Scene()
+    s.eye, s.width, s.height = [0.0, 0.0, 6.0], size, size
+    s.ortho, s.background, s.ambient = [-1.0, -1.0, 1.0, 1.0], [0.0, 0.0, 0.0], 0.4
+    lt = np.asarray(light_tris, np.float64).reshape(-1, 3)
+    s.light_obj, s.light_color = Obj.from_arrays(lt, np.arange(len(lt)).reshape(-1, 3)), [1.0, 0.9, 0.8]
+    s.npaths, s.tonemapping, s.seed = 1, 1.0, 1
+    for tris, rgb in objects:
+        v = np.asarray(tris, np.float64).reshape(-1, 3)
+        s.objects.append({"geometry": Obj.from_arrays(v, np.arange(len(v)).reshape(-1, 3)), "red": rgb[0], "green": rgb[1],
+                          "blue": rgb[2], "ka": 0.3, "kd": 0.6, "ks": 0.3, "kt": 0.0, "n": 3.0})
+    return s
+
+
+def test_lbvh_with_a_single_object_triangle_uses_the_full_tree():
+    """One object triangle: there is no occlusion tree (it needs 2 leaves), shadow rays walk the full tree and skip
+    the light by its reference indices.  LBVH == brute force in FP64, records included."""
+    wall = [[[-2, -2, -3], [2, -2, -3], [0, 2.5, -3]]]
+    light = [[[-0.5, 1.5, -1], [0.5, 1.5, -1], [0, 1.5, -2]], [[-0.5, 1.5, -1], [0, 1.5, -2], [-1, 1.5, -2]]]
+    sc = _mini_scene([(wall, (0.9, 0.5, 0.2))], light)
+    rb = ptb.Renderer(sc, device=0, accel=ptb.ACCEL_BRUTE)
+    rl = ptb.Renderer(sc, device=0, accel=ptb.ACCEL_LBVH)
+    for prec in (ptb.PREC_FP64, ptb.PREC_FP32):
+        a, ra = rb.trace_paths(4, 3, seed=2, precision=prec, records=True)
+        b, rb_ = rl.trace_paths(4, 3, seed=2, precision=prec, records=True)
+        ra, rb_ = _np(ra), _np(rb_)
+        for k in ("tri", "lobe", "occ", "leak"):
+            assert np.array_equal(ra[k], rb_[k]), (prec, k)
+        assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=1e-5, atol=1e-6)
+    assert (ra["tri"][:, :, 0] >= 0).any()
+    rb.close(); rl.close()
+
+
+def test_lbvh_duplicate_triangles_resolve_ties_like_the_reference(cornell):
+    """Every Cornell triangle stored twice (identical Morton codes, identical hit distances): the closest hit must be
+    the FIRST copy in reference order (main.py:115), through the LBVH as through the brute-force loop and the oracle."""
+    from pathtracerpython_b200.scene import Obj, Scene
+    dup = Scene()
+    for k in ("eye", "width", "height", "ortho", "background", "ambient", "light_color", "npaths", "tonemapping", "seed"):
+        setattr(dup, k, getattr(cornell, k))
+    dup.light_obj = cornell.light_obj
+    for o in cornell.objects:
+        d = dict(o)
+        t = np.concatenate([o["geometry"].triangles, o["geometry"].triangles])
+        d["geometry"] = Obj.from_arrays(t.reshape(-1, 3), np.arange(len(t) * 3).reshape(-1, 3))
+        dup.objects.append(d)
+    flat = dup.flatten()
+    want, _, _ = oracle.Oracle(flat, 96, 96).primary()
+    for accel in (ptb.ACCEL_BRUTE, ptb.ACCEL_LBVH):
+        r = ptb.Renderer(dup, device=0, accel=accel)
+        for prec in (ptb.PREC_FP32, ptb.PREC_FP64):
+            tri, _ = r.trace_primary(96, 96, precision=prec)
+            assert np.array_equal(tri.cpu().numpy(), want), (accel, prec)
+        r.close()
+    # first copies only: within an object the first half of the triangles
+    hit = want[want >= 0]
+    obj = np.asarray(flat["tri_obj"])[hit]
+    first = np.array([np.flatnonzero(np.asarray(flat["tri_obj"]) == k)[0] for k in range(int(obj.max()) + 1)])
+    n_in = np.array([(np.asarray(flat["tri_obj"]) == k).sum() for k in range(int(obj.max()) + 1)])
+    keep = obj < len(dup.objects)
+    assert ((hit[keep] - first[obj[keep]]) < n_in[obj[keep]] // 2).all()

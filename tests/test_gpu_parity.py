@@ -254,3 +254,40 @@ def test_errors_are_loud(rnd):
     with pytest.raises(ptb.PtbError, match="workspace too small"):
         r2.trace_paths(1, 1)
     r2.close()
+
+
+def test_non_square_frame_radiance_vs_oracle(rnd, flat):
+    """W != H: ray index r = ix * H + iy (utils.py:64-69) and per-pixel radiance follow the reference; only
+    make_image's index arithmetic is replaced for non-square frames."""
+    W, H, spp, nb = 56, 24, 3, 3
+    orc = oracle.Oracle(flat, W, H)
+    want, _, _ = orc.primary()
+    tri, _ = rnd.trace_primary(W, H)
+    assert np.array_equal(tri.cpu().numpy(), want)
+    ref = orc.trace(spp, nb, 31, details=False)["radiance"]
+    acc, _ = rnd.trace_paths(spp, nb, seed=31, width=W, height=H, precision=ptb.PREC_FP64)
+    assert np.abs(acc[:, :3].cpu().numpy() / spp - ref).max() < 1e-5
+    img = rnd.image(acc, W, H).cpu().numpy()
+    assert img.shape == (H, W, 3)
+
+
+def test_pixel_lists_and_ragged_shards(rnd):
+    import torch
+    res, spp, nb = 50, 2, 3                                  # 2500 pixels: tile 64 does not divide it, 3 shards are ragged
+    full, _ = rnd.trace_paths(spp, nb, seed=5, width=res, height=res)
+    merged = torch.zeros_like(full)
+    counts = []
+    for s in range(3):
+        px, _ = rnd.pixels(res, res, s, 3, 64)
+        counts.append(rnd.pixel_count(px))
+        part, _ = rnd.trace_paths(spp, nb, seed=5, width=res, height=res, shard=s, n_shards=3, tile=64)
+        assert part.shape[0] == counts[-1]
+        rnd.scatter(px, part, merged)
+    assert sum(counts) == res * res and len(set(counts)) > 1
+    assert torch.equal(full, merged)
+    # an explicit, unordered pixel list (with a repeated pixel) renders exactly those pixels
+    lst = np.array([2499, 0, 1234, 77, 1234], np.int32)
+    part, _ = rnd.trace_paths(spp, nb, seed=5, width=res, height=res, pixel_list=lst)
+    assert torch.equal(part, full[torch.as_tensor(lst.astype(np.int64), device=full.device)])
+    empty, _ = rnd.trace_paths(spp, nb, seed=5, width=res, height=res, pixel_list=np.zeros(0, np.int32))
+    assert empty.shape[0] == 0
