@@ -215,7 +215,11 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
 // the 64 B nodes, the leaf-ordered TriRec array and the slot -> reference index table.
 // Builds over the first `n` triangles of the scene (reference order): n = n_tri gives the closest-hit tree,
 // n = n_tri_obj the occlusion tree (main.py:42 loops over scene.objects only; the light mesh is last).
-static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
+// The hierarchy is object-major: triangles are ordered by (rank of their object, Morton code inside the object's own
+// box) and the radix tree is built over that 64-bit key, so the top levels separate whole meshes (the reference's
+// scenes are lists of `object file.obj` meshes: walls, blocks) and every mesh gets a subtree with tight boxes - flat
+// for a wall.  n_objs = number of object ids among the n triangles.
+static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
                       const int **ids_out, double *ms_out, cudaStream_t st) {
     DScene &d = s->d;
     cudaEvent_t e0, e1;
@@ -224,6 +228,7 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
     Aabb *tri_box = nullptr, *node_box = nullptr; float4 *centroid = nullptr; unsigned *scene_box = nullptr, *keys[2] = {nullptr, nullptr};
     int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
     unsigned *ghist = nullptr, *flags = nullptr, *totals = nullptr, *d_n = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
+    unsigned *obj_box = nullptr, *morton_orig = nullptr; unsigned long long *key64 = nullptr; float *obj_lo = nullptr, *obj_inv = nullptr; int *rank = nullptr;
     std::vector<void *> tmp;
     auto alloc = [&](void **p, size_t bytes, bool keep) -> int {
         PTB_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));
@@ -239,6 +244,9 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
         (rc = alloc((void **)&node_minref, 4 * (size_t)n, false)) || (rc = alloc((void **)&child, sizeof(int2) * n, false)) ||
         (rc = alloc((void **)&ghist, 4 * (size_t)256 * n_tiles, false)) || (rc = alloc((void **)&totals, 4 * 256, false)) ||
         (rc = alloc((void **)&d_n, 16, false)) || (rc = alloc((void **)&flags, 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&obj_box, 24 * (size_t)n_objs, false)) || (rc = alloc((void **)&morton_orig, 4 * (size_t)n, false)) ||
+        (rc = alloc((void **)&key64, 8 * (size_t)n, false)) || (rc = alloc((void **)&obj_lo, 12 * (size_t)n_objs, false)) ||
+        (rc = alloc((void **)&obj_inv, 12 * (size_t)n_objs, false)) || (rc = alloc((void **)&rank, 4 * (size_t)n_objs, false)) ||
         (rc = alloc((void **)&nodes, sizeof(BvhNode) * (size_t)n, true)) || (rc = alloc((void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true))) {
         for (void *p : tmp) cudaFree(p);
         return rc;
@@ -250,24 +258,68 @@ static int build_lbvh(ptb_scene *s, int n, const TriRec *src_tri, const BvhNode 
         ProfScope ps_(PK_BUILD, st);
         const int g = grid_for((size_t)n, 256, 8);
         k_bounds_init<<<1, 32, 0, st>>>(scene_box);
-        k_tri_bounds<<<g, 256, 0, st>>>(d.verts64, n, tri_box, centroid, scene_box);
-        k_morton<<<g, 256, 0, st>>>(centroid, n, scene_box, keys[0], vals[0]);
+        k_obj_bounds_init<<<grid_for((size_t)n_objs * 6, 256, 1), 256, 0, st>>>(obj_box, n_objs);
+        k_tri_bounds<<<g, 256, 0, st>>>(d.verts64, d.tri_obj, n, tri_box, centroid, scene_box, obj_box);
         g_launches += 3;
-        // 4 passes x 8 bits of the device-count radix sort (ptb_sort.cuh: per-digit row scans, no single-block
-        // scan over all tiles); after an even number of passes the result is back in buffer 0
+        // object boxes -> host: Morton normalisation per object and the rank of every object along the Morton curve of
+        // the object centres (a spatial order for the top levels); PTB_BVH_FLAT=1 keeps one scene-wide Morton order
+        std::vector<unsigned> h_box((size_t)n_objs * 6 + 6);
+        cudaMemcpyAsync(h_box.data(), obj_box, 24 * (size_t)n_objs, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(h_box.data() + (size_t)n_objs * 6, scene_box, 24, cudaMemcpyDeviceToHost, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess) { for (void *p : tmp) cudaFree(p); set_error("LBVH build: bounds pass failed"); return PTB_ERR_CUDA; }
+        auto unorder = [](unsigned o) { unsigned b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; float f; memcpy(&f, &b, 4); return f; };
+        const bool flat = getenv("PTB_BVH_FLAT") != nullptr;
+        float slo[3], shi[3];
+        for (int k = 0; k < 3; ++k) { slo[k] = unorder(h_box[(size_t)n_objs * 6 + k]); shi[k] = unorder(h_box[(size_t)n_objs * 6 + 3 + k]); }
+        std::vector<float> h_lo((size_t)n_objs * 3), h_inv((size_t)n_objs * 3);
+        std::vector<int> h_rank(n_objs, 0);
+        std::vector<std::pair<unsigned, int>> order;
+        auto ex10 = [](unsigned v) { v = (v * 0x00010001u) & 0xFF0000FFu; v = (v * 0x00000101u) & 0x0F00F00Fu; v = (v * 0x00000011u) & 0xC30C30C3u; return (v * 0x00000005u) & 0x49249249u; };
+        for (int o = 0; o < n_objs; ++o) {
+            unsigned code = 0;
+            float ext = 1e-30f, blo3[3], bhi3[3];
+            for (int k = 0; k < 3; ++k) {
+                blo3[k] = unorder(h_box[(size_t)o * 6 + k]); bhi3[k] = unorder(h_box[(size_t)o * 6 + 3 + k]);
+                if (flat || !(bhi3[k] >= blo3[k])) { blo3[k] = slo[k]; bhi3[k] = shi[k]; }   // empty object: any box will do
+                ext = std::max(ext, bhi3[k] - blo3[k]);
+            }
+            for (int k = 0; k < 3; ++k) {
+                const float lo = blo3[k], hi = bhi3[k];
+                h_lo[(size_t)o * 3 + k] = lo;
+                // one scale for the three axes (cubic Morton cells): a tall block must not get tall cells
+                h_inv[(size_t)o * 3 + k] = 1024.0f / (getenv("PTB_BVH_ANISO") ? std::max(hi - lo, 1e-30f) : ext);
+                const float c = (0.5f * (lo + hi) - slo[k]) / std::max(shi[k] - slo[k], 1e-30f) * 1024.0f;
+                code |= ex10((unsigned)std::min(std::max(c, 0.0f), 1023.0f)) << (2 - k);
+            }
+            order.push_back(std::make_pair(code, o));
+        }
+        std::sort(order.begin(), order.end());
+        if (!flat) for (int r = 0; r < n_objs; ++r) h_rank[order[r].second] = r;
+        cudaMemcpyAsync(obj_lo, h_lo.data(), 12 * (size_t)n_objs, cudaMemcpyHostToDevice, st);
+        cudaMemcpyAsync(obj_inv, h_inv.data(), 12 * (size_t)n_objs, cudaMemcpyHostToDevice, st);
+        cudaMemcpyAsync(rank, h_rank.data(), 4 * (size_t)n_objs, cudaMemcpyHostToDevice, st);
+        k_morton<<<g, 256, 0, st>>>(centroid, d.tri_obj, n, obj_lo, obj_inv, keys[0], morton_orig, vals[0]);
+        ++g_launches;
+        // stable LSD radix sort (ptb_sort.cuh): 4 passes x 8 bits on the Morton code, then the object rank on top
         int cur = 0;
         const int rs_blocks = (n_tiles + PS_WARPS - 1) / PS_WARPS;
-        for (int pass = 0; pass < 4; ++pass) {
-            k_ps_hist<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], d_n, 8 * pass, n_tiles, ghist);
+        int rank_passes = 0;
+        if (!flat) for (unsigned m = (unsigned)(n_objs - 1); m; m >>= 8) ++rank_passes;
+        for (int pass = 0; pass < 4 + rank_passes; ++pass) {
+            if (pass == 4) { k_rank_keys<<<g, 256, 0, st>>>(vals[cur], d.tri_obj, rank, n, keys[cur]); ++g_launches; }
+            const int shift = pass < 4 ? 8 * pass : 8 * (pass - 4);
+            k_ps_hist<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], d_n, shift, n_tiles, ghist);
             k_ps_rowscan<<<256, 1024, 0, st>>>(ghist, n_tiles, totals);
-            k_ps_scatter<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], (const unsigned *)vals[cur], d_n, 8 * pass, n_tiles, ghist, totals,
+            k_ps_scatter<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], (const unsigned *)vals[cur], d_n, shift, n_tiles, ghist, totals,
                                                              keys[cur ^ 1], (unsigned *)vals[cur ^ 1]);
             g_launches += 3;
             cur ^= 1;
         }
-        cudaMemcpyAsync(vals[1], vals[0], 4 * (size_t)n, cudaMemcpyDeviceToDevice, st);   // cur == 0 after 4 passes
+        if (cur == 0) cudaMemcpyAsync(vals[1], vals[0], 4 * (size_t)n, cudaMemcpyDeviceToDevice, st);
+        k_key64<<<g, 256, 0, st>>>(vals[1], d.tri_obj, rank, morton_orig, n, key64);
+        ++g_launches;
         cudaMemsetAsync(flags, 0, 4 * (size_t)n, st);
-        k_karras<<<g, 256, 0, st>>>(keys[0], n, child, parent_inner, parent_leaf);
+        k_karras<<<g, 256, 0, st>>>(key64, n, child, parent_inner, parent_leaf);
         k_refit<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, parent_inner, parent_leaf, node_box, node_minref, flags);
         k_pack<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, node_box, node_minref, s->pad, nodes);
         k_gather_tris<<<g, 256, 0, st>>>(n, vals[1], src_tri, tri_sorted);
@@ -442,13 +494,13 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     s->sort_rays = getenv("PTB_NO_SORT") == nullptr;
     s->build_ms = 0.0;
     s->n_nodes = 0;
-    s->pad = (float)(scale * 3.814697265625e-06);   // 2^-18 * scene scale
+    s->pad = (float)(scale * (getenv("PTB_BVH_PAD18") ? 3.814697265625e-06 : 4.76837158203125e-07));   // 2^-21 * scene scale (4 x the FP32 slab error)
     if (accel == PTB_ACCEL_LBVH) {
         const TriRec *ref_order = d.tri;      // the reference-order array stays allocated: source of both gathers
         double ms_all = 0.0, ms_occ = 0.0;
-        if ((rc = build_lbvh(s, n, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, st))) { ptb_scene_destroy(s); return rc; }
+        if ((rc = build_lbvh(s, n, no + 1, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, st))) { ptb_scene_destroy(s); return rc; }
         if (d.n_tri_obj >= 2) {
-            if ((rc = build_lbvh(s, d.n_tri_obj, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, st))) { ptb_scene_destroy(s); return rc; }
+            if ((rc = build_lbvh(s, d.n_tri_obj, no, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, st))) { ptb_scene_destroy(s); return rc; }
         } else {                              // degenerate occlusion set: fall back to the full tree + min-ref pruning
             d.nodes_occ = nullptr; d.tri_occ = nullptr; d.tri_id_occ = nullptr;
         }

@@ -1,6 +1,6 @@
 // ptb_bvh_build.cuh - GPU LBVH build (north_star (1); no reference counterpart):
 //   1. per-triangle bounds + centroid, scene bounds            (k_tri_bounds)
-//   2. 30-bit Morton codes, 10 bits per axis                   (k_morton)
+//   2. 30-bit Morton codes inside each OBJECT's box, object rank above them (k_morton, k_rank_keys, k_key64)
 //   3. LSD radix sort of (code, triangle) pairs, 8 bits/pass   (ptb_sort.cuh: k_ps_hist / k_ps_rowscan / k_ps_scatter)
 //   4. Karras 2012 binary radix tree over the sorted codes     (k_karras)
 //   5. bottom-up AABB refit, second arrival at a node proceeds (k_refit, atomic flags)
@@ -30,10 +30,46 @@ __global__ void k_bounds_init(unsigned *scene_box) {
     else if (threadIdx.x < 6) scene_box[threadIdx.x] = 0u;
 }
 
+// obj_box: 6 ordered uints per object (min xyz, max xyz), initialised like scene_box.  Triangles are stored object by
+// object, so a warp nearly always holds one object: lanes of the same object are folded with match_any and the
+// group leader issues the 6 atomics.
+__global__ void k_obj_bounds_init(unsigned *obj_box, int n_objs) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_objs * 6; i += gridDim.x * blockDim.x) obj_box[i] = (i % 6) < 3 ? 0xffffffffu : 0u;
+}
+
 __global__ void __launch_bounds__(256)
-k_tri_bounds(const double *__restrict__ verts, int n, Aabb *__restrict__ box, float4 *__restrict__ centroid, unsigned *scene_box) {
+k_tri_bounds(const double *__restrict__ verts, const int *__restrict__ tri_obj, int n, Aabb *__restrict__ box, float4 *__restrict__ centroid,
+             unsigned *scene_box, unsigned *obj_box) {
     float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int n_round = (n + 31) & ~31;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n_round; i0 += gridDim.x * blockDim.x) {
+        const bool live = i0 < n;
+        const int i = live ? i0 : n - 1;
+        {   // per-object box
+            const double *v = verts + 9 * (size_t)i;
+            const int obj = live ? tri_obj[i] : -1 - (int)(threadIdx.x & 31);
+            const unsigned peers = __match_any_sync(0xffffffffu, obj);
+            float olo[3], ohi[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                olo[k] = __double2float_rd(fmin(v[k], fmin(v[3 + k], v[6 + k])));
+                ohi[k] = __double2float_ru(fmax(v[k], fmax(v[3 + k], v[6 + k])));
+            }
+            const int leader = __ffs(peers) - 1;
+            if (peers == 0xffffffffu) {          // the common case: whole warp, one object
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    for (int o = 16; o > 0; o >>= 1) {
+                        olo[k] = fminf(olo[k], __shfl_xor_sync(0xffffffffu, olo[k], o));
+                        ohi[k] = fmaxf(ohi[k], __shfl_xor_sync(0xffffffffu, ohi[k], o));
+                    }
+                if ((int)(threadIdx.x & 31) == leader && live)
+                    for (int k = 0; k < 3; ++k) { atomicMin(obj_box + 6 * obj + k, f_order(olo[k])); atomicMax(obj_box + 6 * obj + 3 + k, f_order(ohi[k])); }
+            } else if (live) {
+                for (int k = 0; k < 3; ++k) { atomicMin(obj_box + 6 * obj + k, f_order(olo[k])); atomicMax(obj_box + 6 * obj + 3 + k, f_order(ohi[k])); }
+            }
+        }
+        if (!live) continue;
         const double *v = verts + 9 * (size_t)i;
         Aabb b;
 #pragma unroll
@@ -69,18 +105,35 @@ __device__ __forceinline__ unsigned expand10(unsigned v) {
     return v;
 }
 
+// 30-bit Morton code of the centroid INSIDE THE BOX OF ITS OBJECT (obj_lo / obj_inv: origin and 1024 / extent per
+// object): a flat wall spends its 10 + 10 bits on its own two dimensions instead of on the room's.
 __global__ void __launch_bounds__(256)
-k_morton(const float4 *__restrict__ centroid, int n, const unsigned *__restrict__ scene_box, unsigned *__restrict__ keys, int *__restrict__ vals) {
-    const float lx = f_unorder(scene_box[0]), ly = f_unorder(scene_box[1]), lz = f_unorder(scene_box[2]);
-    const float ex = fmaxf(f_unorder(scene_box[3]) - lx, 1e-30f), ey = fmaxf(f_unorder(scene_box[4]) - ly, 1e-30f),
-                ez = fmaxf(f_unorder(scene_box[5]) - lz, 1e-30f);
+k_morton(const float4 *__restrict__ centroid, const int *__restrict__ tri_obj, int n, const float *__restrict__ obj_lo,
+         const float *__restrict__ obj_inv, unsigned *__restrict__ keys, unsigned *__restrict__ morton_orig, int *__restrict__ vals) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 c = centroid[i];
-        const unsigned x = (unsigned)fminf(fmaxf((c.x - lx) / ex * 1024.f, 0.f), 1023.f);
-        const unsigned y = (unsigned)fminf(fmaxf((c.y - ly) / ey * 1024.f, 0.f), 1023.f);
-        const unsigned z = (unsigned)fminf(fmaxf((c.z - lz) / ez * 1024.f, 0.f), 1023.f);
-        keys[i] = (expand10(x) << 2) | (expand10(y) << 1) | expand10(z);
+        const int o = tri_obj[i];
+        const unsigned x = (unsigned)fminf(fmaxf((c.x - __ldg(obj_lo + 3 * o)) * __ldg(obj_inv + 3 * o), 0.f), 1023.f);
+        const unsigned y = (unsigned)fminf(fmaxf((c.y - __ldg(obj_lo + 3 * o + 1)) * __ldg(obj_inv + 3 * o + 1), 0.f), 1023.f);
+        const unsigned z = (unsigned)fminf(fmaxf((c.z - __ldg(obj_lo + 3 * o + 2)) * __ldg(obj_inv + 3 * o + 2), 0.f), 1023.f);
+        const unsigned m = (expand10(x) << 2) | (expand10(y) << 1) | expand10(z);
+        keys[i] = m; morton_orig[i] = m;
         vals[i] = i;
+    }
+}
+// second sort key: the rank of the triangle's object (objects ordered along the Morton curve of their centres)
+__global__ void __launch_bounds__(256)
+k_rank_keys(const int *__restrict__ vals, const int *__restrict__ tri_obj, const int *__restrict__ rank, int n, unsigned *__restrict__ keys) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) keys[i] = (unsigned)__ldg(rank + tri_obj[vals[i]]);
+}
+// 64-bit hierarchy key of the sorted sequence: object rank above the in-object Morton code, so the radix tree splits
+// objects first (a top level over whole meshes) and each mesh gets its own spatial subtree
+__global__ void __launch_bounds__(256)
+k_key64(const int *__restrict__ vals, const int *__restrict__ tri_obj, const int *__restrict__ rank, const unsigned *__restrict__ morton_orig,
+        int n, unsigned long long *__restrict__ key64) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int t = vals[i];
+        key64[i] = ((unsigned long long)(unsigned)__ldg(rank + tri_obj[t]) << 32) | morton_orig[t];
     }
 }
 
@@ -89,16 +142,16 @@ k_morton(const float4 *__restrict__ centroid, int n, const unsigned *__restrict_
 
 // ---------------------------------------------------------------- Karras hierarchy
 // delta(i, j) = common-prefix length of (code_i, i) and (code_j, j); -1 outside [0, n)
-__device__ __forceinline__ int lbvh_delta(const unsigned *__restrict__ keys, int n, int i, int j) {
+__device__ __forceinline__ int lbvh_delta(const unsigned long long *__restrict__ keys, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
-    const unsigned a = keys[i], b = keys[j];
-    if (a == b) return 32 + __clz((unsigned)i ^ (unsigned)j);
-    return __clz(a ^ b);
+    const unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((unsigned)i ^ (unsigned)j);
+    return __clzll((long long)(a ^ b));
 }
 
 // inner node i in [0, n-1); children encoded: >= 0 inner node, < 0 leaf with sorted position ~c
 __global__ void __launch_bounds__(256)
-k_karras(const unsigned *__restrict__ keys, int n, int2 *__restrict__ child, int *__restrict__ parent_inner, int *__restrict__ parent_leaf) {
+k_karras(const unsigned long long *__restrict__ keys, int n, int2 *__restrict__ child, int *__restrict__ parent_inner, int *__restrict__ parent_leaf) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
         const int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
         const int dmin = lbvh_delta(keys, n, i, i - d);

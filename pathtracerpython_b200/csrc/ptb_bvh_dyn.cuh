@@ -19,6 +19,9 @@
 namespace ptb {
 
 #define PTB_DYN_MIN 20     // refill when fewer lanes than this are still traversing
+#ifndef PTB_SHADOW_ORDER
+#define PTB_SHADOW_ORDER 2  // children of a shadow-ray node: 0 stored order, 1 nearer first, 2 farther first
+#endif
 #ifndef PTB_WW_MIN
 #define PTB_WW_MIN 8       // leave the node loop for the triangle tests when fewer lanes than this are still walking
 #endif
@@ -197,7 +200,18 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                     go0 = go0 && (tf0 >= -lim) && (fmaxf(-tn0, tf0) >= PTB_TMIN_SAFE);
                     go1 = go1 && (tf1 >= -lim) && (fmaxf(-tn1, tf1) >= PTB_TMIN_SAFE);
                 }
-                if (go0 && go1) { stack[sp++] = c1; node = c0; }
+                if (go0 && go1) {
+#if PTB_SHADOW_ORDER == 0
+                    stack[sp++] = c1; node = c0;
+#else
+                    // any-hit order: FARTHER child first.  The boxes around the origin are the expensive ones (every
+                    // ancestor of the shaded point is entered, tilted faces have fat boxes) and they rarely occlude: the
+                    // point's own surface is rejected by the self-hit guard.  Occluders sit away from the origin.
+                    const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
+                    const bool first1 = PTB_SHADOW_ORDER == 2 ? (k1 > k0) : (k1 < k0);
+                    stack[sp++] = first1 ? c0 : c1; node = first1 ? c1 : c0;
+#endif
+                }
                 else if (go0 || go1) node = go0 ? c0 : c1;
                 else if (sp > 0) node = stack[--sp];
                 else node = PTB_WW_DONE;

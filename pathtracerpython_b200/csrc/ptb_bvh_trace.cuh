@@ -22,8 +22,8 @@ template <typename T> struct LineBox {
     }
 };
 // parameter interval of the line inside the box (no clamping to t >= 0); NaN-safe via fmin/fmax.
-// t = plane * (1/d) - o * (1/d) as one FMA per plane: its error is <= 2^-23 * scale * |1/d|, 1/32 of what the box padding
-// (2^-18 * scale in space, i.e. 2^-18 * scale * |1/d| in t) leaves, so no triangle the exact test accepts is culled.
+// t = plane * (1/d) - o * (1/d) as one FMA per plane: its error is <= 2^-23 * scale * |1/d|, 1/4 of what the box padding
+// (2^-21 * scale in space, i.e. 2^-21 * scale * |1/d| in t) leaves, so no triangle the exact test accepts is culled.
 __device__ __forceinline__ void slab(const LineBox<float> &r, float lx, float ly, float lz, float hx, float hy, float hz, float &tn, float &tf) {
     const float ax = fmaf(lx, r.ix, r.bx), bx = fmaf(hx, r.ix, r.bx);
     const float ay = fmaf(ly, r.iy, r.by), by = fmaf(hy, r.iy, r.by);
