@@ -19,6 +19,9 @@
 namespace ptb {
 
 #define PTB_DYN_MIN 20     // refill when fewer lanes than this are still traversing
+#ifndef PTB_BVH_MIN_BLOCKS
+#define PTB_BVH_MIN_BLOCKS 10
+#endif
 #ifndef PTB_SHADOW_ORDER
 #define PTB_SHADOW_ORDER 2  // children of a shadow-ray node: 0 stored order, 1 nearer first, 2 farther first
 #endif
@@ -44,7 +47,7 @@ __device__ __forceinline__ unsigned claim_work(bool want, unsigned *work, unsign
 // ---------------------------------------------------------------- closest hit
 // PHYS (physical mode): ray semantics, only t > tmin counts; boxes behind the origin are skipped.
 template <bool TRACK, bool COUNT, bool PHYS = false>
-__global__ void __launch_bounds__(PTB_BVH_THREADS)
+__global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
 k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__restrict__ qd, const unsigned *__restrict__ d_count,
                     float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
                     unsigned *work, const unsigned *__restrict__ order) {
@@ -145,7 +148,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
 // PHYS: plain any-hit ray query for every light sample (t in (tmin, distance)); the outcome array holds the
 // sample's FLOAT weight written by the shade kernel and an occluded sample is zeroed (ptb_phys.cuh).
 template <bool COUNT, bool PHYS = false>
-__global__ void __launch_bounds__(PTB_BVH_THREADS)
+__global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
 k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const unsigned *__restrict__ d_count,
                    int *__restrict__ sh_res, int cap, unsigned *work, const unsigned *__restrict__ order) {
     // occlusion tree: object triangles only (main.py:42); the full tree + min-ref pruning when it does not exist

@@ -155,7 +155,7 @@ class Renderer:
         p.samples_per_batch = int(samples_per_batch)
         if accum is None:
             accum = torch.zeros((npix, 4), dtype=torch.float32, device=self.device)
-        if npix == 0 or n_rays <= 0:          # empty pixel set / sample range: nothing to launch
+        if (pixel_list is not None and npix == 0) or n_rays <= 0:   # empty pixel list / sample range: nothing to launch
             return accum, None
         rec, rec_t = None, None
         if records:
