@@ -92,36 +92,40 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 go0 = go0 && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
                 go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             }
-#pragma unroll
-            for (int side = 0; side < 2; ++side) {
-                const bool go = side ? go1 : go0;
-                const int c = side ? c1 : c0;
-                if (go && c < 0) {
-                    const int slot = ~c;
-                    const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
-                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-                    const float eps = TRACK ? __ldg(reinterpret_cast<const float *>(tp + 3)) : 0.f;
-                    if (COUNT) nt++;
-                    float t, dt = 0.f; bool edge = false;
-                    const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
-                    const int ref = side ? m1 : m0;            // leaf: the min-ref field is the triangle itself
-                    const float a = fabsf(t);
-                    const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
-                    if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
-                        if (TRACK) {
-                            if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
-                            uc.best_dt = dt; uc.best_edge = edge;
-                        }
-                        h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref;
-                    } else if (TRACK && (hit || edge)) {
-                        uc.comp_lo = fminf(uc.comp_lo, a - dt);
+            // leaf children: one shared test block walked up to twice, so lanes with a single leaf child (either side)
+            // run it together instead of the warp stepping through a copy per side
+            const bool leaf0 = go0 && c0 < 0, leaf1 = go1 && c1 < 0;
+            int lc = leaf0 ? c0 : c1, lref = leaf0 ? m0 : m1;
+            int n_leaf = (leaf0 ? 1 : 0) + (leaf1 ? 1 : 0);
+#pragma unroll 1
+            while (n_leaf > 0) {
+                const int slot = ~lc;
+                const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
+                const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                const float eps = TRACK ? __ldg(reinterpret_cast<const float *>(tp + 3)) : 0.f;
+                if (COUNT) nt++;
+                float t, dt = 0.f; bool edge = false;
+                const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
+                const int ref = lref;                      // leaf: the min-ref field is the triangle itself
+                const float a = fabsf(t);
+                const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
+                if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
+                    if (TRACK) {
+                        if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
+                        uc.best_dt = dt; uc.best_edge = edge;
                     }
+                    h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref;
+                } else if (TRACK && (hit || edge)) {
+                    uc.comp_lo = fminf(uc.comp_lo, a - dt);
                 }
+                lc = c1; lref = m1;                        // a second leaf can only be child 1
+                --n_leaf;
             }
             go0 = go0 && c0 >= 0; go1 = go1 && c1 >= 0;
             if (go0 && go1) {
                 const bool first1 = k1 < k0;
-                stack[sp++] = first1 ? c0 : c1;
+                const int later = first1 ? c0 : c1;
+                stack[sp++] = later;
                 node = first1 ? c1 : c0;
             } else if (go0 || go1) {
                 node = go0 ? c0 : c1;
@@ -212,7 +216,8 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                     // point's own surface is rejected by the self-hit guard.  Occluders sit away from the origin.
                     const float k0 = PHYS ? fmaxf(tn0, 0.f) : near_abs(tn0, tf0), k1 = PHYS ? fmaxf(tn1, 0.f) : near_abs(tn1, tf1);
                     const bool first1 = PTB_SHADOW_ORDER == 2 ? (k1 > k0) : (k1 < k0);
-                    stack[sp++] = first1 ? c0 : c1; node = first1 ? c1 : c0;
+                    const int later = first1 ? c0 : c1;
+                    stack[sp++] = later; node = first1 ? c1 : c0;
 #endif
                 }
                 else if (go0 || go1) node = go0 ? c0 : c1;
