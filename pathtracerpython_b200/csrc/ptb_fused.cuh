@@ -25,6 +25,9 @@
 
 namespace ptb {
 
+#ifndef PTB_FUSED_VOTE
+#define PTB_FUSED_VOTE 0      // warp-vote plane skipping after the first bounce (incoherent warps: it never skips)
+#endif
 #ifndef PTB_FUSED_MIN_BLOCKS
 #define PTB_FUSED_MIN_BLOCKS 4
 #endif
@@ -116,7 +119,7 @@ k_bounce_planes32(DScene sc, PlaneScene ps, BatchInfo bi, const float4 *__restri
             light_samples32(sc, bi.seed, r, sample, (uint32_t)bi.bounce, P, ld);
             const float4 pk = make_float4(P.x, P.y, P.z, k);
             bool occ0, occ1; int leak_ref;
-            shadow_planes32(planes, ps.n_occ, pk, ld[0], ld[1], ld[2], shaded, occ0, occ1, leak_ref);
+            shadow_planes32<false, FIRST || PTB_FUSED_VOTE>(planes, ps.n_occ, pk, ld[0], ld[1], ld[2], shaded, occ0, occ1, leak_ref);
             if (shaded) {
                 ++n_shaded;
                 const bool occ2 = leak_ref != 0x7fffffff;
@@ -155,7 +158,7 @@ k_bounce_planes32(DScene sc, PlaneScene ps, BatchInfo bi, const float4 *__restri
                 if (!last) {
                     o_new = make_float4(P.x, P.y, P.z, knew);
                     d_new = make_float4(wv.x, wv.y, wv.z, __int_as_float(id));
-                    closest_planes32(planes, ps.n_planes, o_new, d_new, shaded, t_new, tri_new);
+                    closest_planes32<false, PTB_FUSED_VOTE != 0>(planes, ps.n_planes, o_new, d_new, shaded, t_new, tri_new);
                     if (shaded) {
                         ++n_traced;
                         bool light_hit = false;

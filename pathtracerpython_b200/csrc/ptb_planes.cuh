@@ -54,12 +54,15 @@ __device__ __forceinline__ float bary_min(const float4 q1, const float4 q2, floa
 // ---------------------------------------------------------------- closest hit
 // Warp-collective (votes): all 32 lanes must call it together; lanes with live == false never keep a group alive.
 // PHYS (physical mode): a RAY query, only hits in front of the origin count (t > tmin).
-template <bool PHYS = false>
+// VOTE = false: no warp votes, straight-line predicated code the compiler can unroll and pipeline - for incoherent warps
+// (every bounce after the first) some lane always needs every plane, so the votes only cost instructions and latency.
+template <bool PHYS = false, bool VOTE = true>
 __device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_planes, const float4 a, const float4 b, bool live,
                                                  float &best_t, int &best_ref) {
     float best_a = live ? 3.0e38f : 0.f;
     best_t = 0.f;
     best_ref = -1;
+#pragma unroll 2
     for (int g = 0; g < n_planes; ++g) {
         const float4 nd = planes[g].nd;
         const float dn = fmaf(nd.z, b.z, fmaf(nd.y, b.y, nd.x * b.x));
@@ -67,7 +70,7 @@ __device__ __forceinline__ void closest_planes32(const PlaneRec *planes, int n_p
         const float t = on * rcp_approx(dn);
         const float at = fabsf(t);
         const bool ok = (fabsf(dn) > PTB_ZERO_F) && ((PHYS ? t : at) > PTB_TMIN_F) && (at < best_a);
-        if (!__any_sync(0xffffffffu, ok)) continue;
+        if (VOTE && !__any_sync(0xffffffffu, ok)) continue;
         const float px = fmaf(t, b.x, a.x), py = fmaf(t, b.y, a.y), pz = fmaf(t, b.z, a.z);
         if (planes[g].kind) {                   // warp-uniform
             float u;
@@ -111,7 +114,7 @@ k_closest_planes32(DScene sc, PlaneScene ps, const float4 *__restrict__ qo, cons
 // Warp-collective.  pk.xyz = shaded point, d0..d2 = unit directions (w = squared distance to the light
 // sample).  occ0 / occ1: sample occluded; leak_ref: lowest reference index among the occluders of sample
 // 2, 0x7fffffff if it is unoccluded (-1 for dead lanes).
-template <bool PHYS = false>
+template <bool PHYS = false, bool VOTE = true>
 __device__ __forceinline__ void shadow_planes32(const PlaneRec *planes, int n_occ, const float4 pk, const float4 d0, const float4 d1,
                                                 const float4 d2, bool live, bool &occ0, bool &occ1, int &leak_ref) {
     occ0 = !live; occ1 = !live;            // dead lanes never keep a group alive
@@ -129,7 +132,7 @@ __device__ __forceinline__ void shadow_planes32(const PlaneRec *planes, int n_oc
         const bool ok0 = !occ0 && (fabsf(dn0) > PTB_ZERO_F) && (s0 >= PTB_ZERO_F) && (s0 < d0.w) && (!PHYS || t0 > 0.f);
         const bool ok1 = !occ1 && (fabsf(dn1) > PTB_ZERO_F) && (s1 >= PTB_ZERO_F) && (s1 < d1.w) && (!PHYS || t1 > 0.f);
         const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dn2) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w) && (!PHYS || t2 > 0.f);
-        if (!__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
+        if (VOTE && !__any_sync(0xffffffffu, ok0 || ok1 || ok2)) continue;
         const float p0x = fmaf(t0, d0.x, pk.x), p0y = fmaf(t0, d0.y, pk.y), p0z = fmaf(t0, d0.z, pk.z);
         const float p1x = fmaf(t1, d1.x, pk.x), p1y = fmaf(t1, d1.y, pk.y), p1z = fmaf(t1, d1.z, pk.z);
         const float p2x = fmaf(t2, d2.x, pk.x), p2y = fmaf(t2, d2.y, pk.y), p2z = fmaf(t2, d2.z, pk.z);
