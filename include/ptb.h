@@ -27,7 +27,10 @@ typedef enum {
     PTB_ERR_ARG = -1,      /* bad argument */
     PTB_ERR_CUDA = -2,     /* CUDA runtime error (text in ptb_last_error) */
     PTB_ERR_NOMEM = -3,    /* workspace too small */
-    PTB_ERR_UNSUPPORTED = -4
+    PTB_ERR_UNSUPPORTED = -4,
+    PTB_ERR_IO = -5,           /* ptb_obj_parse: file cannot be opened / read (the reference: OSError) */
+    PTB_ERR_PARSE = -6,        /* ptb_obj_parse: token the reference's float()/int() rejects (ValueError) */
+    PTB_ERR_PARSE_INDEX = -7   /* ptb_obj_parse: blank last line (the reference: IndexError, scene_reader.py:31) */
 } ptb_status;
 
 /* Flattened scene = the data the reference keeps in `Scene` / `Obj` objects
@@ -167,6 +170,17 @@ int ptb_profile_read(double *ms_per_kind, uint64_t *launches_per_kind);
 /* FP32 FMA issue peak of the current device, measured with a register-resident FMA microbenchmark
  * (roofline denominator for the compute-bound small-scene kernels). */
 int ptb_fp32_peak(double *tflops, void *stream);
+
+/* replaces Obj(path) (scene_reader.py:49-104; line cleaning :29-46) for meshes of 10^6..10^7 triangles:
+ * multi-threaded host parse of `v` / `f` lines with the reference's rules (comments, tabs, polygons fanned
+ * about their first vertex, negative = relative indices, 'i/j/k' rejected).  On PTB_OK *verts holds
+ * 3*n_verts doubles (bit-identical to Python's float()), *faces 3*n_faces vertex indices, *skipped (may be
+ * passed as NULL) the cleaned text of every line with an unknown keyword, '\n'-separated, for the caller to
+ * report as the reference does (:102-104).  All three are released with ptb_obj_free.  threads <= 0: all
+ * host cores.  Pure host code: needs no device. */
+int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts, int64_t **faces, int64_t *n_faces,
+                  char **skipped, int threads);
+void ptb_obj_free(void *p);
 
 int ptb_counters_read(const ptb_scene *scene, ptb_counters *out, void *stream); /* synchronises stream */
 int ptb_counters_reset(const ptb_scene *scene, void *stream);

@@ -13,7 +13,8 @@ FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES, FLAG_PHYSICAL, FL
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
-           "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace"]
+           "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
+           "ptb_obj_parse", "ptb_obj_free"]
 
 
 class PtbError(RuntimeError):
@@ -82,6 +83,10 @@ def lib():
         L.ptb_pixel_count.argtypes = [C.POINTER(Pixels)]
         L.ptb_profile_enable.argtypes = [C.c_int]
         L.ptb_fp32_peak.argtypes = [C.POINTER(C.c_double), C.c_void_p]
+        L.ptb_obj_parse.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p),
+                                    C.POINTER(C.c_int64), C.POINTER(C.c_void_p), C.c_int]
+        L.ptb_obj_free.argtypes = [C.c_void_p]
+        L.ptb_obj_free.restype = None
         L.ptb_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
@@ -90,6 +95,39 @@ def lib():
 def check(rc, what):
     if rc != 0:
         raise PtbError(f"{what} failed ({rc}): {lib().ptb_last_error().decode()}")
+
+
+ERR_IO, ERR_PARSE, ERR_PARSE_INDEX = -5, -6, -7
+
+
+def obj_parse(path, threads=0):
+    """ptb_obj_parse -> (vertexes float64 [n,3], faces int64 [m,3], [cleaned text of skipped lines]).
+    Raises what the reference's parser raises: OSError, ValueError ('i/j/k', bad numbers), IndexError."""
+    import numpy as np
+    L = lib()
+    v, f, sk = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    nv, nf = C.c_int64(), C.c_int64()
+    rc = L.ptb_obj_parse(os.fsencode(path), C.byref(v), C.byref(nv), C.byref(f), C.byref(nf), C.byref(sk), threads)
+    if rc != 0:
+        msg = L.ptb_last_error().decode()
+        if rc == ERR_IO:
+            raise FileNotFoundError(msg)
+        if rc == ERR_PARSE:
+            raise ValueError(msg)
+        if rc == ERR_PARSE_INDEX:
+            raise IndexError("string index out of range")
+        raise PtbError(f"ptb_obj_parse failed ({rc}): {msg}")
+    try:
+        verts = np.ctypeslib.as_array(C.cast(v, C.POINTER(C.c_double)), (nv.value * 3,)).reshape(-1, 3).copy() \
+            if nv.value else np.zeros((0, 3), np.float64)
+        faces = np.ctypeslib.as_array(C.cast(f, C.POINTER(C.c_int64)), (nf.value * 3,)).reshape(-1, 3).copy() \
+            if nf.value else np.zeros((0, 3), np.int64)
+        skipped = C.string_at(sk).decode(errors="replace").split("\n")[:-1] if sk.value else []
+    finally:
+        for p in (v, f, sk):
+            if p.value:
+                L.ptb_obj_free(p)
+    return verts, faces, skipped
 
 
 def profile_enable(on=True):

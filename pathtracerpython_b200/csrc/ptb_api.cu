@@ -530,3 +530,4 @@ extern "C" int ptb_scene_info(const ptb_scene *s, int32_t *accel, int32_t *n_nod
 extern "C" int64_t ptb_pixel_count(const ptb_pixels *px) { return px ? pixel_count(px) : 0; }
 
 #include "ptb_api_render.inl"
+#include "ptb_obj.inl"

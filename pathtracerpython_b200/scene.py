@@ -36,13 +36,41 @@ def _tokens(line):
     return [t for t in line.split(" ") if t]
 
 
+def _native_parser_wanted(path, min_bytes):
+    import os
+    from . import _lib
+    try:
+        return os.path.getsize(path) >= min_bytes and os.path.exists(_lib.LIB_PATH)
+    except OSError:
+        return False                    # let the Python parser raise the reference's error
+
+
 class Obj:
     """Triangle mesh (scene_reader.py:49-104).  triangles [n,3,3], normals [n,3], areas [n] float64."""
 
-    def __init__(self, path, quiet=True):
+    NATIVE_MIN_BYTES = 1 << 16          # smaller files: the Python parser below is as quick as a library call
+
+    def __init__(self, path, quiet=True, native=None):
+        """native: None = ptb_obj_parse (libptb.so, multi-threaded) for files over NATIVE_MIN_BYTES when the
+        library is built, True / False = force one parser.  Both give the same arrays and the same errors
+        (tests/test_obj_native.py)."""
         if not quiet:
             print("Reading " + path)
         self.path = path
+        if native is None:
+            native = _native_parser_wanted(path, self.NATIVE_MIN_BYTES)
+        if native:
+            from . import _lib
+            self.vertexes, self.faces, skipped = _lib.obj_parse(path)
+            for line in skipped:
+                tok = _tokens(line.replace("\t", " "))
+                print(f"{path}\n\tSkipping command '{tok[0]}' ! \n\tParameters: {tok[1:]}")
+        else:
+            self.vertexes, self.faces = self._parse_python(path)
+        self._finish()
+
+    @staticmethod
+    def _parse_python(path):
         verts, faces = [], []
         for line in _clean_lines(path):
             tok = _tokens(line)
@@ -62,9 +90,8 @@ class Obj:
                     faces.append(tuple(face))
             else:
                 print(f"{path}\n\tSkipping command '{tok[0]}' ! \n\tParameters: {tok[1:]}")
-        self.vertexes = np.asarray([v[:3] for v in verts], np.float64).reshape(-1, 3)
-        self.faces = np.asarray(faces, np.int64).reshape(-1, 3)
-        self._finish()
+        return (np.asarray([v[:3] for v in verts], np.float64).reshape(-1, 3),
+                np.asarray(faces, np.int64).reshape(-1, 3))
 
     @classmethod
     def from_arrays(cls, vertexes, faces, path="<arrays>"):
