@@ -147,6 +147,28 @@ def test_one_million_triangles_build_and_consistency(cornell):
     r.close()
 
 
+def test_ten_million_triangles_fp32_retrace_equals_fp64(cornell):
+    """Config 5's scene (9 999 392 triangles; 1.1 GB of device records): the exactness property at the size where
+    triangles are 1/559 of a wall and the padding of 2^-21 x scene size matters most."""
+    t = synth.tessellate(cornell, 559)
+    r = ptb.Renderer(t, device=0)
+    assert r.info()["accel"] == "lbvh" and t.flatten()["verts"].shape[0] == 9999392
+    a, _ = r.trace_primary(768, 768)
+    b, _ = r.trace_primary(768, 768, precision=ptb.PREC_FP64)
+    a, b = a.cpu().numpy(), b.cpu().numpy()
+    assert np.array_equal(a, b)
+    assert (a >= 0).mean() > 0.9
+    # hit triangles refine the hit triangles of the untessellated box: parent id = id // 559^2
+    coarse = ptb.Renderer(cornell, device=0)
+    c, _ = coarse.trace_primary(768, 768)
+    c = c.cpu().numpy()
+    inner = (a >= 0) & (c >= 0)
+    assert (a[inner] // (559 * 559) == c[inner]).mean() > 0.999         # pixels on an edge of the coarse mesh may differ
+    acc, _ = r.trace_paths(1, 3, seed=1, width=256, height=256)
+    assert bool(np.isfinite(acc.cpu().numpy()).all())
+    r.close(); coarse.close()
+
+
 # ------------------------------------------------------------------ edge cases
 def _mini_scene(objects, light_tris, size=24):
     from pathtracerpython_b200.scene import Obj, Scene
