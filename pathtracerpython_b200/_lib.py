@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libptb.so")
+LIB_PATH = os.environ.get("PTB_LIB_PATH") or os.path.join(_HERE, "libptb.so")      # override: A/B builds of the same source
 
 PREC_FP32, PREC_FP64 = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2

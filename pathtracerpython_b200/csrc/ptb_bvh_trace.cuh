@@ -48,12 +48,27 @@ __device__ __forceinline__ double far_abs(double tn, double tf) { return fmax(-t
 // the FP32 ray parameter carries ~1e-5 of error, so prune only below 3.0e-3
 #define PTB_TMIN_SAFE 3.0e-3f
 
+// 256-bit read-only load (sm_100: LDG.E.256): the L1 tag stage serves scattered accesses one lane and one instruction
+// at a time, so a 64 B node or triangle record costs two requests per lane this way instead of four LDG.128.
+// p must be 32 B aligned (nodes and records are 64 B structs in their own cudaMalloc).
+#ifndef PTB_LD256
+#define PTB_LD256 1
+#endif
+__device__ __forceinline__ void ld256(const void *p, float4 &lo, float4 &hi) {
+#if PTB_LD256
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "l"(p));
+#else
+    lo = __ldg(reinterpret_cast<const float4 *>(p)); hi = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+#endif
+}
+
 struct NodeBoxes { float4 a, b, c; int4 d; };
 __device__ __forceinline__ NodeBoxes ld_node(const BvhNode *nodes, int i) {
     const float4 *p = reinterpret_cast<const float4 *>(nodes + i);
     NodeBoxes n;
-    n.a = __ldg(p); n.b = __ldg(p + 1); n.c = __ldg(p + 2);
-    const float4 w = __ldg(p + 3);
+    float4 w;
+    ld256(p, n.a, n.b); ld256(p + 2, n.c, w);
     n.d = make_int4(__float_as_int(w.x), __float_as_int(w.y), __float_as_int(w.z), __float_as_int(w.w));
     return n;
 }
