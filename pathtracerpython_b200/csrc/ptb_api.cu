@@ -454,6 +454,17 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         const double c = cdf[i];              // pick_random_triangle: cum[i] <= uniform(0, total)  (utils.py:30, 38)
         light_thr[i] = i == 0 ? 0u : first_m([&](unsigned m) { return 0.0 + (total - 0.0) * ((double)m * 5.9604644775390625e-08) >= c; });
     }
+    // bucket table over m: with B >= n_light_tri buckets a pick needs 1-2 threshold reads instead of log2(n)
+    int light_shift = 24;
+    while (light_shift > 2 && (1 << (24 - light_shift)) < desc->n_light_tri) --light_shift;
+    const int n_bucket = 1 << (24 - light_shift);
+    std::vector<int> light_bucket((size_t)n_bucket + 1);
+    for (int b = 0, i = 0; b <= n_bucket; ++b) {            // largest i with thr[i] <= b << shift (thr is non-decreasing, thr[0] = 0)
+        const unsigned long long edge = (unsigned long long)b << light_shift;
+        while (i + 1 < desc->n_light_tri && light_thr[i + 1] <= edge) ++i;
+        light_bucket[b] = i;
+    }
+    d.light_shift = light_shift;
     std::vector<int> lobe_thr(no + 1, 0), pow_int(no + 1, -1);
     for (int k = 0; k < no; ++k) {
         const double kd = desc->mat[8 * k + 4], ks = desc->mat[8 * k + 5], ne = desc->mat[8 * k + 7];
@@ -478,7 +489,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     if ((rc = upload(s, mat32, &d.mat32, st)) || (rc = upload(s, lv, &d.light_v32, st)) ||
         (rc = upload(s, mat64, &d.mat64, st)) || (rc = upload(s, cdf, &d.light_cdf, st)) ||
         (rc = upload(s, obj_first, &d.obj_first, st)) ||
-        (rc = upload(s, light_thr, &d.light_thr, st)) || (rc = upload(s, lobe_thr, &d.obj_lobe_thr, st)) || (rc = upload(s, pow_int, &d.obj_pow_int, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
+        (rc = upload(s, light_thr, &d.light_thr, st)) || (rc = upload(s, light_bucket, &d.light_bucket, st)) || (rc = upload(s, lobe_thr, &d.obj_lobe_thr, st)) || (rc = upload(s, pow_int, &d.obj_pow_int, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
     }

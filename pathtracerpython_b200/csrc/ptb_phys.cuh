@@ -110,7 +110,7 @@ k_shade_phys32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const flo
 #pragma unroll
             for (int s = 0; s < 3; ++s) {
                 const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);
-                const int li = pick_light_int(sc.light_thr, sc.n_light_tri, w.x >> 8);
+                const int li = pick_light_int(sc, w.x >> 8);
                 const float su = sqrtf(u01<float>(w.y)), u2 = u01<float>(w.z);
                 const float wa = 1.0f - su, wb = su * (1.0f - u2), wc = su * u2;          // area-uniform barycentrics
                 const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);

@@ -35,6 +35,8 @@ struct DScene {
     const double *light_cdf;  // [n_light_tri+1] running sums of light_obj.areas (utils.py:31-35)
     const int *tri_obj;       // [n_tri]
     const unsigned *light_thr; // [n_light_tri] integer form of the light CDF: pick = largest i with thr[i] <= (x >> 8)
+    const int *light_bucket;   // [2^k + 1] bucket b = m >> light_shift -> largest i with thr[i] <= b << light_shift: the
+    int light_shift;           //   pick lies in [bucket[b], bucket[b+1]], a 1-2 step search instead of log2(n) dependent loads
     const int *obj_lobe_thr;  // [n_obj+1] diffuse lobe iff (x >> 8) < thr  (exact integer form of main.py:240-241)
     const int *obj_pow_int;   // [n_obj+1] exponent n if it is a small non-negative integer, else -1
     const int *obj_first;     // [n_obj+2] first reference triangle of every object (light = n_obj), then n_tri

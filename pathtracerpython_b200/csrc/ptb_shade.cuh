@@ -83,9 +83,11 @@ __device__ __forceinline__ int pick_light(const double *cdf, int n, double x) {
 
 // integer form of the same pick: thr[i] = smallest 24-bit m whose product total * m * 2^-24 reaches
 // cum[i] (built on the host in FP64), so the choice is bit-identical and needs no FP64 on the device
-__device__ __forceinline__ int pick_light_int(const unsigned *thr, int n, unsigned m) {
-    if (n == 2) return m >= __ldg(thr + 1) ? 1 : 0;
-    int lo = 0, hi = n;
+__device__ __forceinline__ int pick_light_int(const DScene &sc, unsigned m) {
+    const unsigned *thr = sc.light_thr;
+    if (sc.n_light_tri == 2) return m >= __ldg(thr + 1) ? 1 : 0;
+    const unsigned b = m >> sc.light_shift;
+    int lo = __ldg(sc.light_bucket + b), hi = __ldg(sc.light_bucket + b + 1) + 1;      // thr[lo] <= m, answer in [lo, hi)
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
         if (__ldg(thr + mid) <= m) lo = mid; else hi = mid;
@@ -106,7 +108,7 @@ __device__ __forceinline__ void light_samples32(const DScene &sc, uint32_t seed,
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const uint4 w = rng4(seed, r, sample, bounce, (uint32_t)s);
-        const int li = pick_light_int(sc.light_thr, sc.n_light_tri, w.x >> 8);
+        const int li = pick_light_int(sc, w.x >> 8);
         const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
         const float inv = rcp_approx((c0 + c1) + c2);
         const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
