@@ -201,7 +201,9 @@ def run_ours(a):
     ctr = r.counters()
     clk = clocks.summary() if rank == 0 else None
 
-    # ---- e2e: host scene arrays in, host image out, every step (scene upload + BVH/records build included)
+    # ---- e2e: host scene arrays (page-locked) in, host image out, every step (scene upload + BVH/records build included)
+    scene.flatten(pin=True)
+
     def e2e_step():
         rr = ptb.Renderer(scene, device=local)
         img = step(rr)

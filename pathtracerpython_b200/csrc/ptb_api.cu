@@ -452,7 +452,19 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     std::vector<unsigned> light_thr(desc->n_light_tri);
     for (int i = 0; i < desc->n_light_tri; ++i) {
         const double c = cdf[i];              // pick_random_triangle: cum[i] <= uniform(0, total)  (utils.py:30, 38)
-        light_thr[i] = i == 0 ? 0u : first_m([&](unsigned m) { return 0.0 + (total - 0.0) * ((double)m * 5.9604644775390625e-08) >= c; });
+        // smallest m with total * (m * 2^-24) >= c: start from the real-number estimate and walk to the switch point
+        // (the product is monotone in m), a couple of evaluations instead of a 24-step bisection per light triangle
+        auto reached = [&](long long m) { return 0.0 + (total - 0.0) * ((double)m * 5.9604644775390625e-08) >= c; };
+        long long m;
+        const double guess = c / total * 16777216.0;
+        if (!(total > 0.0) || !(guess >= 0.0) || !(guess <= 16777216.0)) m = reached(0) ? 0 : (reached(1ll << 24) ? -1 : 1ll << 24);
+        else m = (long long)guess;
+        if (m < 0) m = first_m([&](unsigned mm) { return reached(mm); });          // degenerate areas: plain bisection
+        else {
+            while (m > 0 && reached(m - 1)) --m;
+            while (m < (1ll << 24) && !reached(m)) ++m;
+        }
+        light_thr[i] = i == 0 ? 0u : (unsigned)m;
     }
     // bucket table over m: with B >= n_light_tri buckets a pick needs 1-2 threshold reads instead of log2(n)
     int light_shift = 24;

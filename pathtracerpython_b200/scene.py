@@ -174,12 +174,21 @@ class Scene:
                 f"objects={len(self.objects)} npaths={self.npaths} seed={self.seed}>")
 
     # ---- boundary: flatten into the arrays of ptb_scene_desc (include/ptb.h)
-    def flatten(self, refresh=False):
+    def flatten(self, refresh=False, pin=False):
         """-> dict of the packed arrays of ptb_scene_desc.  The result is cached on the scene (building it copies
-        every triangle once: ~1 s for 10 M triangles); pass refresh=True after editing the scene in place."""
-        if not refresh and getattr(self, "_flat", None) is not None:
-            return self._flat
-        self._flat = self._flatten()
+        every triangle once: ~1 s for 10 M triangles); pass refresh=True after editing the scene in place.
+        pin=True moves the big arrays into page-locked host memory (once; needs a CUDA device), so that every
+        Renderer(scene) uploads them at full PCIe / C2C rate instead of through the driver's staging buffer."""
+        if refresh or getattr(self, "_flat", None) is None:
+            self._flat = self._flatten()
+            self._pinned = None
+        if pin and getattr(self, "_pinned", None) is None:
+            import torch
+            self._pinned = {}
+            for k in ("verts", "normals", "tri_obj", "light_areas"):
+                t = torch.from_numpy(self._flat[k]).pin_memory()
+                self._pinned[k] = t                      # owns the page-locked allocation behind the numpy view
+                self._flat[k] = t.numpy()
         return self._flat
 
     def _flatten(self):
