@@ -302,16 +302,12 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
         ++g_launches;
         // stable LSD radix sort (ptb_sort.cuh): 4 passes x 8 bits on the Morton code, then the object rank on top
         int cur = 0;
-        const int rs_blocks = (n_tiles + PS_WARPS - 1) / PS_WARPS;
         int rank_passes = 0;
         if (!flat) for (unsigned m = (unsigned)(n_objs - 1); m; m >>= 8) ++rank_passes;
         for (int pass = 0; pass < 4 + rank_passes; ++pass) {
             if (pass == 4) { k_rank_keys<<<g, 256, 0, st>>>(vals[cur], d.tri_obj, rank, n, keys[cur]); ++g_launches; }
             const int shift = pass < 4 ? 8 * pass : 8 * (pass - 4);
-            k_ps_hist<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], d_n, shift, n_tiles, ghist);
-            k_ps_rowscan<<<256, 1024, 0, st>>>(ghist, n_tiles, totals);
-            k_ps_scatter<<<rs_blocks, PS_WARPS * 32, 0, st>>>(keys[cur], (const unsigned *)vals[cur], d_n, shift, n_tiles, ghist, totals,
-                                                             keys[cur ^ 1], (unsigned *)vals[cur ^ 1]);
+            ps_sort_pass(keys[cur], (const unsigned *)vals[cur], d_n, shift, n_tiles, ghist, totals, keys[cur ^ 1], (unsigned *)vals[cur ^ 1], st);
             g_launches += 3;
             cur ^= 1;
         }

@@ -280,13 +280,10 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         if (sorting) {      // order the survivors by the Morton key of their new origin (ptb_sort.cuh)
             ProfScope ps_(PK_SORT, st);
             const SortBufs &sb = q.sort;
-            const int blocks = (sb.tiles_max + PS_WARPS - 1) / PS_WARPS;
             int cur = 0;
             for (int pass = 0; pass < 3; ++pass) {
-                k_ps_hist<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist);
-                k_ps_rowscan<<<256, 1024, 0, st>>>(sb.ghist, sb.tiles_max, sb.totals);
-                k_ps_scatter<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass,
-                                                              sb.tiles_max, sb.ghist, sb.totals, sb.keys[cur ^ 1], sb.vals[cur ^ 1]);
+                ps_sort_pass(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist, sb.totals,
+                             pass < 2 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
                 g_launches += 3;
                 cur ^= 1;
             }
@@ -365,13 +362,10 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
         if (sorting && b + 1 < p->bounces) {
             ProfScope ps_(PK_SORT, st);
             const SortBufs &sb = q.sort;
-            const int blocks = (sb.tiles_max + PS_WARPS - 1) / PS_WARPS;
             int cur = 0;
             for (int pass = 0; pass < 3; ++pass) {
-                k_ps_hist<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist);
-                k_ps_rowscan<<<256, 1024, 0, st>>>(sb.ghist, sb.tiles_max, sb.totals);
-                k_ps_scatter<<<blocks, PS_WARPS * 32, 0, st>>>(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass,
-                                                              sb.tiles_max, sb.ghist, sb.totals, sb.keys[cur ^ 1], sb.vals[cur ^ 1]);
+                ps_sort_pass(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist, sb.totals,
+                             pass < 2 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
                 g_launches += 3;
                 cur ^= 1;
             }

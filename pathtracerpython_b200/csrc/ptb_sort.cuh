@@ -16,8 +16,9 @@
 
 namespace ptb {
 
-#define PS_TILE 2048       // elements per warp tile
+#define PS_TILE 8192       // elements per block tile
 #define PS_WARPS 8
+#define PS_SUB (PS_TILE / PS_WARPS)     // consecutive elements per warp: keeps the scatter stable
 
 __device__ __forceinline__ unsigned ps_expand8(unsigned v) {   // 8 bits -> every third bit
     v = (v * 0x00010001u) & 0xFF0000FFu;
@@ -39,15 +40,20 @@ __global__ void __launch_bounds__(PS_WARPS * 32)
 k_ps_hist(const unsigned *__restrict__ keys, const unsigned *__restrict__ d_n, int shift, int tiles_max, unsigned *__restrict__ ghist) {
     __shared__ unsigned s_h[PS_WARPS][256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * PS_WARPS + warp;
-    if (tile >= tiles_max) return;
+    const int tile = blockIdx.x;
     const unsigned n = *d_n;
     for (int b = lane; b < 256; b += 32) s_h[warp][b] = 0;
     __syncwarp();
-    const unsigned beg = (unsigned)tile * PS_TILE, end = min(n, beg + PS_TILE);
-    for (unsigned i = beg + lane; i < end; i += 32) atomicAdd(&s_h[warp][(keys[i] >> shift) & 255u], 1u);
-    __syncwarp();
-    for (int b = lane; b < 256; b += 32) ghist[(size_t)b * tiles_max + tile] = s_h[warp][b];
+    const unsigned beg = (unsigned)tile * PS_TILE;
+    if (beg < n) {
+        const unsigned end = min(n, beg + PS_TILE);
+        for (unsigned i = beg + threadIdx.x; i < end; i += PS_WARPS * 32) atomicAdd(&s_h[warp][(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    unsigned c = 0;
+#pragma unroll
+    for (int w = 0; w < PS_WARPS; ++w) c += s_h[w][threadIdx.x];
+    ghist[(size_t)threadIdx.x * tiles_max + tile] = c;
 }
 
 // one block per digit value: exclusive scan of its row of tile counts in place, row total to totals[bin]
@@ -71,54 +77,95 @@ __global__ void __launch_bounds__(1024) k_ps_rowscan(unsigned *ghist, int tiles_
     if (threadIdx.x == 1023) totals[blockIdx.x] = s_part[1023];
 }
 
-// stable scatter; vals == nullptr means the identity permutation (first pass)
+// Stable scatter of one block tile; vals == nullptr means the identity permutation (first pass), keys_out == nullptr
+// skips the key write (last pass).  The tile is first ordered by digit in shared memory (warp sub-tiles in order,
+// iterations in order, lanes in order), so each digit leaves the block as ONE contiguous run (PS_TILE / 256 = 32
+// elements on average): full 128 B lines instead of a 4 B write per element into 256 places.
+#define PS_SCATTER_SMEM (2 * PS_TILE * sizeof(unsigned))
 __global__ void __launch_bounds__(PS_WARPS * 32)
 k_ps_scatter(const unsigned *__restrict__ keys, const unsigned *__restrict__ vals, const unsigned *__restrict__ d_n, int shift,
              int tiles_max, const unsigned *__restrict__ ghist, const unsigned *__restrict__ totals,
              unsigned *__restrict__ keys_out, unsigned *__restrict__ vals_out) {
-    __shared__ unsigned s_off[PS_WARPS][256];
-    __shared__ unsigned s_base[256];
+    extern __shared__ __align__(16) unsigned s_stage[];           // [PS_TILE] keys, [PS_TILE] values, in digit order
+    __shared__ unsigned s_cnt[PS_WARPS][256];                     // per warp and digit: count, then running local position
+    __shared__ unsigned s_gbase[256];                             // digit -> global position of local position 0
+    __shared__ unsigned s_w[PS_WARPS];
+    unsigned *s_k = s_stage, *s_v = s_stage + PS_TILE;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * PS_WARPS + warp;
+    const int tile = blockIdx.x;
     const unsigned n = *d_n;
-    if ((unsigned)blockIdx.x * PS_WARPS * PS_TILE >= n) return;    // whole block past the live count
-    {   // exclusive scan of the 256 digit totals (one value per thread, PS_WARPS * 32 == 256)
-        const unsigned v = totals[threadIdx.x];
-        unsigned x = v;
-        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-        __shared__ unsigned s_w[PS_WARPS];
-        if (lane == 31) s_w[warp] = x;
-        __syncthreads();
-        unsigned before = 0;
-        for (int w = 0; w < warp; ++w) before += s_w[w];
-        s_base[threadIdx.x] = before + x - v;
-        __syncthreads();
-    }
-    if (tile >= tiles_max) return;
-    for (int b = lane; b < 256; b += 32) s_off[warp][b] = s_base[b] + ghist[(size_t)b * tiles_max + tile];
+    const unsigned beg = (unsigned)tile * PS_TILE;
+    if (beg >= n) return;                                         // whole block past the live count
+    const unsigned end = min(n, beg + PS_TILE);
+    const unsigned sub_beg = beg + (unsigned)warp * PS_SUB, sub_end = min(end, sub_beg + PS_SUB);
+    for (int b = lane; b < 256; b += 32) s_cnt[warp][b] = 0;
     __syncwarp();
-    const unsigned beg = (unsigned)tile * PS_TILE, end = min(n, beg + PS_TILE);
-    for (unsigned base = beg; base < end; base += 32) {
+    for (unsigned i = sub_beg + lane; i < sub_end; i += 32) atomicAdd(&s_cnt[warp][(keys[i] >> shift) & 255u], 1u);
+    // global start of every digit: exclusive scan of the 256 totals (one per thread, PS_WARPS * 32 == 256)
+    const unsigned tot = totals[threadIdx.x];
+    unsigned x = tot;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    unsigned gstart = x - tot;
+    for (int w = 0; w < warp; ++w) gstart += s_w[w];
+    // this thread's digit: positions of the warps' sub-runs inside the tile's run, and the tile's run inside the digit
+    unsigned mine = 0;
+#pragma unroll
+    for (int w = 0; w < PS_WARPS; ++w) { const unsigned c = s_cnt[w][threadIdx.x]; s_cnt[w][threadIdx.x] = mine; mine += c; }
+    __syncthreads();                                              // s_w is reused
+    unsigned y = mine;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned z = __shfl_up_sync(0xffffffffu, y, o); if (lane >= o) y += z; }
+    if (lane == 31) s_w[warp] = y;
+    __syncthreads();
+    unsigned lstart = y - mine;                                   // local position of the digit's first element
+    for (int w = 0; w < warp; ++w) lstart += s_w[w];
+#pragma unroll
+    for (int w = 0; w < PS_WARPS; ++w) s_cnt[w][threadIdx.x] += lstart;
+    s_gbase[threadIdx.x] = gstart + ghist[(size_t)threadIdx.x * tiles_max + tile] - lstart;
+    __syncthreads();
+    for (unsigned base = sub_beg; base < sub_end; base += 32) {
         const unsigned i = base + lane;
-        const bool live = i < end;
+        const bool live = i < sub_end;
         const unsigned k = live ? keys[i] : 0u;
         const unsigned v = live ? (vals ? vals[i] : i) : 0u;
         const unsigned d = live ? ((k >> shift) & 255u) : 256u + lane;   // dead lanes match nobody
         const unsigned peers = __match_any_sync(0xffffffffu, d);
         const unsigned rank = __popc(peers & ((1u << lane) - 1u));
         unsigned pos = 0;
-        if (live) pos = s_off[warp][d] + rank;
+        if (live) pos = s_cnt[warp][d] + rank;
         __syncwarp();
-        if (live && rank == 0) s_off[warp][d] += __popc(peers);
+        if (live && rank == 0) s_cnt[warp][d] += __popc(peers);
         __syncwarp();
-        if (live) { keys_out[pos] = k; vals_out[pos] = v; }
+        if (live) { s_k[pos] = k; s_v[pos] = v; }
+    }
+    __syncthreads();
+    const unsigned m = end - beg;
+    for (unsigned p = threadIdx.x; p < m; p += PS_WARPS * 32) {
+        const unsigned k = s_k[p];
+        const unsigned g = s_gbase[(k >> shift) & 255u] + p;
+        if (keys_out) keys_out[g] = k;
+        vals_out[g] = s_v[p];
     }
 }
+
+// one pass of the LSD sort on `st`: n is read from *d_n on the device, tiles = ceil(capacity / PS_TILE)
+static inline void ps_sort_pass(const unsigned *keys, const unsigned *vals, const unsigned *d_n, int shift, int tiles,
+                                unsigned *ghist, unsigned *totals, unsigned *keys_out, unsigned *vals_out, cudaStream_t st);
 
 struct SortBufs {
     unsigned *keys[2], *vals[2];   // keys[0] is written by the shade kernel; the sorted order ends in vals[1]
     unsigned *ghist, *totals;
     int tiles_max;
 };
+
+static inline void ps_sort_pass(const unsigned *keys, const unsigned *vals, const unsigned *d_n, int shift, int tiles,
+                                unsigned *ghist, unsigned *totals, unsigned *keys_out, unsigned *vals_out, cudaStream_t st) {
+    static bool once = false;
+    if (!once) { cudaFuncSetAttribute(k_ps_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PS_SCATTER_SMEM); once = true; }
+    k_ps_hist<<<tiles, PS_WARPS * 32, 0, st>>>(keys, d_n, shift, tiles, ghist);
+    k_ps_rowscan<<<256, 1024, 0, st>>>(ghist, tiles, totals);
+    k_ps_scatter<<<tiles, PS_WARPS * 32, PS_SCATTER_SMEM, st>>>(keys, vals, d_n, shift, tiles, ghist, totals, keys_out, vals_out);
+}
 
 }  // namespace ptb
