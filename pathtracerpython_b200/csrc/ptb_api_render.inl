@@ -281,13 +281,13 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             ProfScope ps_(PK_SORT, st);
             const SortBufs &sb = q.sort;
             int cur = 0;
-            for (int pass = 0; pass < 3; ++pass) {
+            for (int pass = 0; pass < PS_PASSES; ++pass) {
                 ps_sort_pass(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist, sb.totals,
-                             pass < 2 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
+                             pass < PS_PASSES - 1 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
                 g_launches += 3;
                 cur ^= 1;
             }
-            order = sb.vals[1];     // 3 passes: 0 -> 1 -> 0 -> 1
+            order = sb.vals[PS_PASSES & 1];     // buffers alternate, pass 0 writes vals[1]
             PTB_LAUNCHED(); --g_launches;
         }
         { ProfScope ps_(PK_SHADOW, st);
@@ -363,13 +363,13 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
             ProfScope ps_(PK_SORT, st);
             const SortBufs &sb = q.sort;
             int cur = 0;
-            for (int pass = 0; pass < 3; ++pass) {
+            for (int pass = 0; pass < PS_PASSES; ++pass) {
                 ps_sort_pass(sb.keys[cur], pass ? sb.vals[cur] : nullptr, q.count + b + 1, 8 * pass, sb.tiles_max, sb.ghist, sb.totals,
-                             pass < 2 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
+                             pass < PS_PASSES - 1 ? sb.keys[cur ^ 1] : nullptr, sb.vals[cur ^ 1], st);
                 g_launches += 3;
                 cur ^= 1;
             }
-            order = sb.vals[1];
+            order = sb.vals[PS_PASSES & 1];
             PTB_LAUNCHED(); --g_launches;
         }
         { ProfScope ps_(PK_SHADOW, st);

@@ -38,6 +38,9 @@ namespace ptb {
 #ifndef PTB_FLAT_STEP_CLOSEST
 #define PTB_FLAT_STEP_CLOSEST 0
 #endif
+#ifndef PTB_SHADOW_GROUP
+#define PTB_SHADOW_GROUP 32
+#endif
 #define PTB_WW_DONE ((int)0x80000000)   // traversal state: nothing left (leaf codes are ~slot > INT_MIN)
 
 // warp-wide claim of new work items for the lanes with want == true; returns the claimed index or
@@ -185,7 +188,13 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
     const BvhNode *__restrict__ nodes = sc.nodes_occ ? sc.nodes_occ : sc.nodes;
     const TriRec *__restrict__ tris = sc.nodes_occ ? sc.tri_occ : sc.tri;
     const unsigned paths = *d_count;
+#if PTB_SHADOW_GROUP
+    // work items in groups of PTB_SHADOW_GROUP paths x 3 samples: the lanes that finish sample s of a group of neighbouring
+    // paths claim sample s + 1 of the same paths next, while the nodes those paths walk are still in this SM's L1
+    const unsigned count = ((paths + PTB_SHADOW_GROUP - 1u) / PTB_SHADOW_GROUP) * (3u * PTB_SHADOW_GROUP);
+#else
     const unsigned count = 3u * paths;
+#endif
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
     int sp = 0, node = 0, found = 0x7fffffff, found_obj = -1;
@@ -198,9 +207,16 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
         if (!exhausted) {
             const bool want = item == 0xffffffffu;
             const unsigned idx = claim_work(want, work, count);
+#if PTB_SHADOW_GROUP
+            const unsigned grp = idx / (3u * PTB_SHADOW_GROUP), rem = idx - grp * (3u * PTB_SHADOW_GROUP);
+            const unsigned s = rem / PTB_SHADOW_GROUP, jj = grp * PTB_SHADOW_GROUP + (rem - s * PTB_SHADOW_GROUP);
+            if (want && idx != 0xffffffffu && jj < paths) {
+                item = idx;
+#else
             if (want && idx != 0xffffffffu) {
                 item = idx;
                 const unsigned s = idx / paths, jj = idx - s * paths;    // sample-major: neighbouring lanes, neighbouring paths
+#endif
                 const unsigned j = order ? order[jj] : jj;
                 out_slot = s * (unsigned)cap + j;
                 const float4 pk = sh_p[j], dv = sh_d[out_slot];
@@ -298,7 +314,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
         if ((threadIdx.x & 31) == 0) { atomicAdd(sc.counters + CTR_NODES_SH, (unsigned long long)nn); atomicAdd(sc.counters + CTR_TRIS_SH, (unsigned long long)nt); }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        atomicAdd(sc.counters + CTR_SHADOW, (unsigned long long)count);
+        atomicAdd(sc.counters + CTR_SHADOW, (unsigned long long)(3u * paths));
         atomicAdd(sc.counters + CTR_SHADED, (unsigned long long)paths);
     }
 }

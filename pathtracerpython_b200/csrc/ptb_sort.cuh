@@ -20,19 +20,24 @@ namespace ptb {
 #define PS_WARPS 8
 #define PS_SUB (PS_TILE / PS_WARPS)     // consecutive elements per warp: keeps the scatter stable
 
-__device__ __forceinline__ unsigned ps_expand8(unsigned v) {   // 8 bits -> every third bit
+// Morton key of a point, PS_KEY_BITS per axis; lo / inv = scene box origin and 256 / extent per axis
+#ifndef PS_KEY_BITS
+#define PS_KEY_BITS 8
+#endif
+#define PS_PASSES ((3 * PS_KEY_BITS + 7) / 8)
+__device__ __forceinline__ unsigned ps_expand10(unsigned v) {  // 10 bits -> every third bit
     v = (v * 0x00010001u) & 0xFF0000FFu;
     v = (v * 0x00000101u) & 0x0F00F00Fu;
     v = (v * 0x00000011u) & 0xC30C30C3u;
     v = (v * 0x00000005u) & 0x49249249u;
     return v;
 }
-// 24-bit Morton key of a point; lo / inv = scene box origin and 256 / extent per axis
 __device__ __forceinline__ unsigned ps_key(float x, float y, float z, const float *lo, const float *inv) {
-    const unsigned ix = (unsigned)fminf(fmaxf((x - lo[0]) * inv[0], 0.f), 255.f);
-    const unsigned iy = (unsigned)fminf(fmaxf((y - lo[1]) * inv[1], 0.f), 255.f);
-    const unsigned iz = (unsigned)fminf(fmaxf((z - lo[2]) * inv[2], 0.f), 255.f);
-    return (ps_expand8(ix) << 2) | (ps_expand8(iy) << 1) | ps_expand8(iz);
+    const float s = (float)(1 << (PS_KEY_BITS - 8)), top = (float)((1 << PS_KEY_BITS) - 1);
+    const unsigned ix = (unsigned)fminf(fmaxf((x - lo[0]) * (inv[0] * s), 0.f), top);
+    const unsigned iy = (unsigned)fminf(fmaxf((y - lo[1]) * (inv[1] * s), 0.f), top);
+    const unsigned iz = (unsigned)fminf(fmaxf((z - lo[2]) * (inv[2] * s), 0.f), top);
+    return (ps_expand10(ix) << 2) | (ps_expand10(iy) << 1) | ps_expand10(iz);
 }
 
 // per-tile digit histogram, bin-major: ghist[bin * tiles_max + tile]; tiles past the live count write zeros
