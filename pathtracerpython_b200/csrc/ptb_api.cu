@@ -337,6 +337,7 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
 }
 
 extern "C" const char *ptb_last_error(void) { return g_err; }
+namespace ptb { static int planes_optin_smem(); }     // ptb_api_render.inl
 extern "C" int ptb_version(void) { return 100; }
 
 extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out) {
@@ -508,6 +509,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     d.ambient = desc->ambient;
     d.light_total = total;
     s->planes.n_planes = (int)planes.size(); s->planes.n_occ = n_occ;
+    if (accel == PTB_ACCEL_BRUTE && (rc = planes_optin_smem())) { ptb_scene_destroy(s); return rc; }
     s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
     s->bvh_dynamic = getenv("PTB_BVH_STATIC") == nullptr;
     s->sort_rays = getenv("PTB_NO_SORT") == nullptr;

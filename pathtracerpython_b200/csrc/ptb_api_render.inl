@@ -3,6 +3,21 @@
 
 namespace ptb {
 
+// The plane list of a 512-triangle soup (up to 512 records of 96 B) exceeds the 48 KB a kernel gets without asking
+static int planes_optin_smem() {
+    static bool done = false;
+    if (done) return PTB_OK;
+    const int bytes = (int)(PTB_BRUTE_MAX_TRI * sizeof(PlaneRec) + 16);
+    PTB_CUDA(cudaFuncSetAttribute(k_closest_planes32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute(k_closest_planes32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute(k_shadow_planes32, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute(k_shadow_planes_phys32, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done = true;
+    return PTB_OK;
+}
+
 // FP64 re-trace of uncertain FP32 primary rays (bounce 0: queue position == path id).
 __global__ void __launch_bounds__(128)
 k_retrace64(DScene sc, PixelMap pm, int npix, const unsigned *__restrict__ unc_count, const int *__restrict__ unc_list,

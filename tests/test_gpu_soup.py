@@ -88,6 +88,33 @@ def test_soup_200_both_back_ends_vs_oracle(accel):
     check_against_oracle(soup_scene(200, 11), accel, 96, 3, 4, 77, 5e-3)
 
 
+def test_soup_512_planes_fill_shared_memory():
+    """512 triangles, no two coplanar: 512 plane records = 49 168 B of dynamic shared memory, more than a kernel
+    gets without opting in."""
+    sc = soup_scene(509, 14)
+    geo = sc.objects[0]["geometry"]
+    v = geo.vertexes.copy()
+    v[0:18] += np.random.default_rng(1).normal(0.0, 0.2, (18, 3))          # undo the degenerate / duplicate / coplanar cases
+    sc.objects[0]["geometry"] = Obj.from_arrays(v, geo.faces)
+    lv = sc.light_obj.vertexes.copy()
+    lv[3, 1] = 2.7                                                         # the light's quad is no longer planar
+    sc.light_obj = Obj.from_arrays(lv, sc.light_obj.faces)
+    flat = sc.flatten(refresh=True)
+    assert flat["verts"].shape[0] == 512
+    r = ptb.Renderer(sc, device=0, accel=ptb.ACCEL_BRUTE)
+    want, _, _ = oracle.Oracle(flat, 64, 64).primary()
+    tri, _ = r.trace_primary(64, 64)
+    assert np.array_equal(tri.cpu().numpy(), want)
+    ref = oracle.Oracle(flat, 32, 32).trace(2, 3, 2)
+    _, rec = r.trace_paths(2, 3, seed=2, width=32, height=32, records=True)
+    rec = _np(rec)
+    ok = _sig(rec, ref)
+    live = ref["tri"] > -2
+    assert (~ok & live).sum() / live.sum() < 5e-3
+    assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
+    r.close()
+
+
 def test_soup_5000_lbvh_vs_oracle():
     check_against_oracle(soup_scene(5000, 12, n_obj=7, size=0.35), ptb.ACCEL_LBVH, 96, 2, 3, 5, 5e-3)
 
