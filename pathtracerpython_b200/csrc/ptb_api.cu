@@ -350,7 +350,9 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     }
     cudaStream_t st = (cudaStream_t)stream;
     int accel = desc->accel;
-    if (accel == PTB_ACCEL_AUTO) accel = desc->n_tri <= PTB_BRUTE_MAX_TRI ? PTB_ACCEL_BRUTE : PTB_ACCEL_LBVH;
+    // measured on random soups (scratch/soup_speed.py): the plane list in shared memory wins up to ~256 triangles
+    // (2.0 vs 1.4 Gsamples/s at 64, 255 vs 207 Msamples/s at 256), the LBVH from ~400 on (119 vs 163 at 512)
+    if (accel == PTB_ACCEL_AUTO) accel = desc->n_tri <= PTB_BRUTE_AUTO_TRI ? PTB_ACCEL_BRUTE : PTB_ACCEL_LBVH;
     if (accel == PTB_ACCEL_BRUTE && desc->n_tri > PTB_BRUTE_MAX_TRI) {
         set_error("brute-force traversal holds at most %d triangles in shared memory", PTB_BRUTE_MAX_TRI);
         return PTB_ERR_UNSUPPORTED;

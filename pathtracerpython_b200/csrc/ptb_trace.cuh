@@ -14,6 +14,7 @@
 namespace ptb {
 
 #define PTB_BRUTE_MAX_TRI 512     // 32 KB of TriRec in shared memory
+#define PTB_BRUTE_AUTO_TRI 320    // PTB_ACCEL_AUTO: brute force (plane list) up to here, LBVH above
 #define PTB_TRACE_THREADS 256
 
 __device__ __forceinline__ void stage_tris(TriRec *s_tri, const TriRec *g_tri, int n) {
