@@ -5,7 +5,7 @@
 //   4. Karras 2012 binary radix tree over the sorted codes     (k_karras)
 //   5. bottom-up AABB refit, second arrival at a node proceeds (k_refit, atomic flags)
 //   6. pack 64 B nodes holding BOTH children's boxes           (k_pack)
-// Boxes are rounded outward and inflated by 2^-18 * scene scale so FP32 slab tests never cull a
+// Boxes are rounded outward and inflated by 2^-21 * scene scale (4 x the FMA slab error) so FP32 slab tests never cull a
 // triangle whose reference test would accept.
 #pragma once
 #include "ptb_scene.cuh"
