@@ -181,6 +181,11 @@ int ptb_fp32_peak(double *tflops, void *stream);
 int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts, int64_t **faces, int64_t *n_faces,
                   char **skipped, int threads);
 void ptb_obj_free(void *p);
+/* Companion writer for generated meshes (no reference counterpart: the reference only reads): `v` lines with the
+ * shortest decimals that parse back to the same doubles, then 1-based `f` lines.  header (may be NULL) becomes a
+ * leading `# ...` comment. */
+int ptb_obj_write(const char *path, const double *verts, int64_t n_verts, const int64_t *faces, int64_t n_faces,
+                  const char *header);
 
 int ptb_counters_read(const ptb_scene *scene, ptb_counters *out, void *stream); /* synchronises stream */
 int ptb_counters_reset(const ptb_scene *scene, void *stream);

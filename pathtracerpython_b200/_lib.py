@@ -14,7 +14,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
-           "ptb_obj_parse", "ptb_obj_free"]
+           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write"]
 
 
 class PtbError(RuntimeError):
@@ -87,6 +87,7 @@ def lib():
                                     C.POINTER(C.c_int64), C.POINTER(C.c_void_p), C.c_int]
         L.ptb_obj_free.argtypes = [C.c_void_p]
         L.ptb_obj_free.restype = None
+        L.ptb_obj_write.argtypes = [C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p]
         L.ptb_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
@@ -128,6 +129,17 @@ def obj_parse(path, threads=0):
             if p.value:
                 L.ptb_obj_free(p)
     return verts, faces, skipped
+
+
+def obj_write(path, vertexes, faces, header=""):
+    """ptb_obj_write: float64 [n,3] vertices and 0-based int64 [m,3] faces -> .obj text with repr-exact decimals."""
+    import numpy as np
+    v = np.ascontiguousarray(vertexes, np.float64).reshape(-1, 3)
+    f = np.ascontiguousarray(faces, np.int64).reshape(-1, 3)
+    rc = lib().ptb_obj_write(os.fsencode(path), v.ctypes.data, v.shape[0], f.ctypes.data, f.shape[0], header.encode())
+    if rc == ERR_IO:
+        raise OSError(lib().ptb_last_error().decode())
+    check(rc, "ptb_obj_write")
 
 
 def profile_enable(on=True):

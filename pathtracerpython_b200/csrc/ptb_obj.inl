@@ -186,3 +186,43 @@ extern "C" int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts,
 }
 
 extern "C" void ptb_obj_free(void *p) { free(p); }
+
+// Writer for generated meshes (synth.write_obj): "v x y z" lines with the shortest decimals that read back to the same
+// doubles (std::to_chars, what Python's repr() prints up to notation), then "f i j k" lines, 1-based.
+extern "C" int ptb_obj_write(const char *path, const double *verts, int64_t n_verts, const int64_t *faces, int64_t n_faces,
+                             const char *header) {
+    if (!path || (n_verts && !verts) || (n_faces && !faces)) { set_error("ptb_obj_write: null argument"); return PTB_ERR_ARG; }
+    FILE *fp = fopen(path, "wb");
+    if (!fp) { set_error("ptb_obj_write: cannot open %s", path); return PTB_ERR_IO; }
+    std::vector<char> buf;
+    buf.reserve(1 << 22);
+    auto flush = [&]() { bool ok = buf.empty() || fwrite(buf.data(), 1, buf.size(), fp) == buf.size(); buf.clear(); return ok; };
+    bool ok = true;
+    if (header && *header) { buf.push_back('#'); buf.push_back(' '); buf.insert(buf.end(), header, header + strlen(header)); buf.push_back('\n'); }
+    char tmp[40];
+    for (int64_t i = 0; i < n_verts && ok; ++i) {
+        buf.push_back('v');
+        for (int k = 0; k < 3; ++k) {
+            buf.push_back(' ');
+            const double x = verts[3 * i + k];
+            auto r = std::to_chars(tmp, tmp + sizeof(tmp), x);
+            buf.insert(buf.end(), tmp, r.ptr);
+        }
+        buf.push_back('\n');
+        if (buf.size() > (1u << 22) - 256) ok = flush();
+    }
+    for (int64_t i = 0; i < n_faces && ok; ++i) {
+        buf.push_back('f');
+        for (int k = 0; k < 3; ++k) {
+            buf.push_back(' ');
+            auto r = std::to_chars(tmp, tmp + sizeof(tmp), (long long)(faces[3 * i + k] + 1));
+            buf.insert(buf.end(), tmp, r.ptr);
+        }
+        buf.push_back('\n');
+        if (buf.size() > (1u << 22) - 256) ok = flush();
+    }
+    ok = flush() && ok;
+    ok = fclose(fp) == 0 && ok;
+    if (!ok) { set_error("ptb_obj_write: write to %s failed", path); return PTB_ERR_IO; }
+    return PTB_OK;
+}

@@ -7,6 +7,7 @@ import os
 
 import numpy as np
 
+from . import _lib
 from .scene import Obj, Scene
 
 
@@ -51,11 +52,17 @@ def tessellate(scene, n):
 
 
 def write_obj(path, obj):
+    """One `v` line per triangle corner and one `f` line per triangle, decimals that read back bit-exactly.  Meshes of
+    more than a few thousand triangles go through the library's writer (ptb_obj_write) when it is built."""
+    n = len(obj.triangles)
+    if n > 4096 and os.path.exists(_lib.LIB_PATH):
+        _lib.obj_write(path, obj.triangles.reshape(-1, 3), np.arange(3 * n, dtype=np.int64).reshape(-1, 3), f"{n} triangles")
+        return
     with open(path, "w") as f:
-        f.write(f"# {len(obj.triangles)} triangles\n")
+        f.write(f"# {n} triangles\n")
         v = obj.triangles.reshape(-1, 3)
         f.write("".join(f"v {repr(float(a))} {repr(float(b))} {repr(float(c))}\n" for a, b, c in v))
-        f.write("".join(f"f {3 * i + 1} {3 * i + 2} {3 * i + 3}\n" for i in range(len(obj.triangles))))
+        f.write("".join(f"f {3 * i + 1} {3 * i + 2} {3 * i + 3}\n" for i in range(n)))
 
 
 def write_scene(scene, directory, name="scene.sdl"):

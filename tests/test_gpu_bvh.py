@@ -147,6 +147,25 @@ def test_one_million_triangles_build_and_consistency(cornell):
     r.close()
 
 
+def test_one_million_triangle_scene_through_the_file_loader(cornell, tmp_path):
+    """Config 4 as FILES: write the tessellated scene in the reference's .sdl / .obj grammar, load it with Scene(path)
+    (native .obj reader) and render: the same triangles, the same hits, the same radiance as the in-memory scene."""
+    t = synth.tessellate(cornell, 177)
+    path = synth.write_scene(t, str(tmp_path), "c4.sdl")
+    loaded = ptb.Scene(path)
+    fa, fb = t.flatten(), loaded.flatten()
+    assert fa["verts"].shape[0] == 1002528 and np.array_equal(fa["verts"], fb["verts"]) and np.array_equal(fa["tri_obj"], fb["tri_obj"])
+    assert np.array_equal(fa["normals"], fb["normals"]) and np.array_equal(fa["mat"], fb["mat"])
+    ra, rb = ptb.Renderer(t, device=0), ptb.Renderer(loaded, device=0)
+    a, _ = ra.trace_primary(256, 256)
+    b, _ = rb.trace_primary(256, 256)
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+    xa, _ = ra.trace_paths(2, 3, seed=5, width=128, height=128)
+    xb, _ = rb.trace_paths(2, 3, seed=5, width=128, height=128)
+    assert np.array_equal(xa.cpu().numpy(), xb.cpu().numpy())
+    ra.close(); rb.close()
+
+
 def test_ten_million_triangles_fp32_retrace_equals_fp64(cornell):
     """Config 5's scene (9 999 392 triangles; 1.1 GB of device records): the exactness property at the size where
     triangles are 1/559 of a wall and the padding of 2^-21 x scene size matters most."""

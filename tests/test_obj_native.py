@@ -143,6 +143,21 @@ def test_multithreaded_slices_keep_relative_indices(tmp_path):
     assert np.array_equal(f1, np.arange(90000).reshape(-1, 3))
 
 
+def test_writer_round_trips_every_double(tmp_path):
+    rng = np.random.default_rng(3)
+    v = np.concatenate([rng.standard_normal(3000) * 10.0 ** rng.integers(-30, 30, 3000),
+                        np.array([0.0, -0.0, 5e-324, 1.7976931348623157e308, 1e22, 1e23, 0.1, 1 / 3, -1e-5])]).reshape(-1, 3)
+    f = rng.integers(0, len(v), (500, 3))
+    p = str(tmp_path / "w.obj")
+    _lib.obj_write(p, v, f, "round trip")
+    for native in (False, True):
+        o = Obj(p, native=native)
+        assert o.vertexes.tobytes() == v.tobytes() and np.array_equal(o.faces, f)
+    assert open(p).readline() == "# round trip\n"
+    with pytest.raises(OSError):
+        _lib.obj_write("/nonexistent/dir/x.obj", v, f)
+
+
 def test_tessellated_scene_round_trip_is_fast(tmp_path):
     """write_scene -> Scene(path) of a 200K-triangle config-4 style scene: the native parser gives the arrays
     the generator wrote, and is much faster than the interpreter loop."""
