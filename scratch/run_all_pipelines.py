@@ -1,4 +1,5 @@
-"""Small end-to-end runs of every pipeline for compute-sanitizer (memcheck / racecheck / initcheck)."""
+"""Small end-to-end runs of every pipeline (both back ends, FP32 / FP64, fused / separate, physical mode): a quick
+GPU smoke run outside pytest."""
 import sys
 sys.path.insert(0, "."); sys.path.insert(0, "tests")
 import numpy as np
