@@ -129,6 +129,19 @@ int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out);
 int ptb_scene_destroy(ptb_scene *scene);
 int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, double *build_ms);
 
+/* Replicating a built scene to other GPUs instead of rebuilding it (the reference pickles the whole scene into
+ * every pool task, main.py:199-201, 208-216; here one rank builds and the others receive).
+ * ptb_bvh_export copies both hierarchies of an LBVH scene (closest-hit tree over object + light triangles and the
+ * occlusion tree over object triangles: 64 B nodes, leaf-ordered 64 B triangle records, slot -> reference index)
+ * into ONE caller-owned device buffer of ptb_bvh_export_bytes(scene) bytes (0 for a scene without LBVH) that can
+ * travel through a single broadcast.  ptb_bvh_import is ptb_scene_create with the sort / tree / refit kernels
+ * replaced by a device-to-device copy of such a buffer: `desc` must describe the same scene (checked against the
+ * buffer's header: triangle counts, box padding, format version), desc->accel is taken as PTB_ACCEL_LBVH.  The
+ * build is deterministic, so an imported scene renders bit-identically to a built one. */
+size_t ptb_bvh_export_bytes(const ptb_scene *scene);
+int ptb_bvh_export(const ptb_scene *scene, void *d_blob, size_t blob_bytes, void *stream);
+int ptb_bvh_import(const ptb_scene_desc *desc, const void *d_blob, size_t blob_bytes, void *stream, ptb_scene **out);
+
 /* replaces make_screen_pts + make_rays + one round of intersect_objects over all primary rays
  * (utils.py:55-69, main.py:191, 199-204, 83-122).  d_tri[i]: global triangle id or -1; d_t[i]:
  * signed ray parameter of the hit (unit direction) or 0.  n outputs = size of the pixel set. */
@@ -153,6 +166,14 @@ int ptb_trace_paths(const ptb_scene *scene, const ptb_render_params *p, void *d_
  * (slot = r); writes the H x W x 3 u8 image, rows top to bottom. d_workspace >= 64 bytes. */
 int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_rgb,
                 void *d_workspace, void *stream);
+
+/* Opt-in display transform (no counterpart in the reference's code path: it parses the scene keywords `background`
+ * and `tonemapping`, scene_reader.py:158-159, 167-168, and never reads them; ptb_tonemap above is what the reference
+ * does).  Per channel: mean / (mean + tonemapping) (tonemapping == 0: the mean itself), clamped to [0, 1], * 255
+ * truncated; pixels with d_primary_tri[r] < 0 (primary ray left the scene; d_primary_tri may be NULL) show
+ * `background` (3 doubles in [0, 1], NULL = black).  Same frame layout as ptb_tonemap. */
+int ptb_tonemap_scene(const float *d_accum, const int32_t *d_primary_tri, int32_t width, int32_t height,
+                      double tonemapping, const double *background, uint8_t *d_rgb, void *stream);
 
 /* scatter a shard's accumulation buffer (pixel-slot order) into a full-frame buffer (ray-index order) */
 int ptb_scatter_accum(const ptb_pixels *px, const float *d_accum_shard, float *d_accum_full, void *stream);

@@ -7,7 +7,9 @@ ignored: they open windows (PIL viewer, OpenGL debug viewer) and there is no dis
 on this box.  Extras (off by default, the reference ignores these scene keywords, A-Q19):
 `--use-npaths` takes -r from the scene's `npaths`, `--seed` overrides the scene's `seed` as Philox key,
 `--size W H` overrides `size`, `--physical` selects physical mode (ray queries, true tangent frame, RGB
-throughput, refraction for `kt`, Russian roulette; include/ptb.h PTB_FLAG_PHYSICAL), `--aov F.npz` dumps the
+throughput, refraction for `kt`, Russian roulette; include/ptb.h PTB_FLAG_PHYSICAL), `--use-output` saves to the
+scene's `output` file when --out is not given (`.pnm` is written as binary PPM), `--scene-tonemap` applies the scene's
+`tonemapping` / `background` keywords instead of make_image's min/max normalisation, `--aov F.npz` dumps the
 primary-hit buffers (triangle id, ray parameter, hit point, normal, object id) that the reference's debug
 viewer draws (plot.py:28-42, 98-105) - as arrays, there is no window."""
 import argparse
@@ -30,6 +32,8 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=None)
     ap.add_argument("--size", type=int, nargs=2, default=None)
     ap.add_argument("--physical", action="store_true")
+    ap.add_argument("--use-output", action="store_true", help="without --out, save to the scene's `output` file")
+    ap.add_argument("--scene-tonemap", action="store_true", help="use the scene's tonemapping/background keywords")
     ap.add_argument("--aov", default=None, help="write primary-hit AOVs to this .npz")
     a = ap.parse_args(argv)
     scene = Scene(a.scene, quiet=False)
@@ -41,9 +45,11 @@ def main(argv=None):
         r = Renderer(scene)
         np.savez_compressed(a.aov, **r.aovs(w, h))
         r.close()
-    im = render(scene, n_rays, a.n_bounces, seed=a.seed, width=w, height=h, flags=FLAG_PHYSICAL if a.physical else 0)
-    if a.out is not None:
-        im.save(a.out)
+    im = render(scene, n_rays, a.n_bounces, seed=a.seed, width=w, height=h, flags=FLAG_PHYSICAL if a.physical else 0,
+                scene_tonemap=a.scene_tonemap)
+    out = a.out if a.out is not None else (scene.output if a.use_output else None)
+    if out is not None:
+        im.save(out, format="PPM") if out.lower().endswith(".pnm") else im.save(out)
     return 0
 
 

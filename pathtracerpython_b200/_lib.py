@@ -14,7 +14,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
-           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write"]
+           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene"]
 
 
 class PtbError(RuntimeError):
@@ -69,6 +69,10 @@ def lib():
         L.ptb_pixel_count.restype = C.c_int64
         L.ptb_scene_create.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.POINTER(C.c_void_p)]
         L.ptb_scene_destroy.argtypes = [C.c_void_p]
+        L.ptb_bvh_export_bytes.restype = C.c_size_t
+        L.ptb_bvh_export_bytes.argtypes = [C.c_void_p]
+        L.ptb_bvh_export.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ptb_bvh_import.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_void_p)]
         L.ptb_scene_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]
         L.ptb_trace_primary.argtypes = [C.c_void_p, C.POINTER(Pixels), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_size_t, C.c_void_p]
@@ -77,6 +81,8 @@ def lib():
         L.ptb_trace_paths.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
                                       C.POINTER(PathRecords), C.c_void_p]
         L.ptb_tonemap.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptb_tonemap_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.POINTER(C.c_double),
+                                        C.c_void_p, C.c_void_p]
         L.ptb_scatter_accum.argtypes = [C.POINTER(Pixels), C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptb_counters_read.argtypes = [C.c_void_p, C.POINTER(Counters), C.c_void_p]
         L.ptb_counters_reset.argtypes = [C.c_void_p, C.c_void_p]

@@ -340,7 +340,41 @@ extern "C" const char *ptb_last_error(void) { return g_err; }
 namespace ptb { static int planes_optin_smem(); }     // ptb_api_render.inl
 extern "C" int ptb_version(void) { return 100; }
 
+// ---- replicated hierarchies (ptb_bvh_export / ptb_bvh_import): one device buffer = header + six sections
+struct BvhBlobHeader {
+    unsigned magic, version;
+    int n_tri, n_tri_obj, has_occ;
+    float pad;
+    unsigned long long off[6];      // nodes, tri, ids, nodes_occ, tri_occ, ids_occ (bytes from the start of the buffer)
+    unsigned long long total;
+};
+static const unsigned BVH_BLOB_MAGIC = 0x56425450u /* "PTBV" */, BVH_BLOB_VERSION = 1u;
+static BvhBlobHeader bvh_blob_layout(int n_tri, int n_tri_obj, bool has_occ, float pad) {
+    BvhBlobHeader h;
+    memset(&h, 0, sizeof(h));
+    h.magic = BVH_BLOB_MAGIC; h.version = BVH_BLOB_VERSION;
+    h.n_tri = n_tri; h.n_tri_obj = n_tri_obj; h.has_occ = has_occ ? 1 : 0; h.pad = pad;
+    const size_t no = has_occ ? (size_t)n_tri_obj : 0;
+    const size_t bytes[6] = {sizeof(BvhNode) * (size_t)n_tri, sizeof(TriRec) * (size_t)n_tri, 4 * (size_t)n_tri,
+                             sizeof(BvhNode) * no, sizeof(TriRec) * no, 4 * no};
+    size_t at = 256;
+    for (int i = 0; i < 6; ++i) { h.off[i] = at; at += (bytes[i] + 255) & ~(size_t)255; }
+    h.total = at;
+    return h;
+}
+
+static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, size_t blob_bytes, void *stream, ptb_scene **out);
+
 extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out) {
+    return scene_create_impl(desc, nullptr, 0, stream, out);
+}
+
+extern "C" int ptb_bvh_import(const ptb_scene_desc *desc, const void *d_blob, size_t blob_bytes, void *stream, ptb_scene **out) {
+    if (!d_blob || blob_bytes < 256) { set_error("ptb_bvh_import: no hierarchy buffer"); return PTB_ERR_ARG; }
+    return scene_create_impl(desc, d_blob, blob_bytes, stream, out);
+}
+
+static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, size_t blob_bytes, void *stream, ptb_scene **out) {
     if (!desc || !out) { set_error("ptb_scene_create: null argument"); return PTB_ERR_ARG; }
     if (desc->n_tri <= 0 || desc->n_tri_obj < 0 || desc->n_tri_obj > desc->n_tri || desc->n_obj <= 0 ||
         desc->n_light_tri != desc->n_tri - desc->n_tri_obj || desc->n_light_tri <= 0 || !desc->verts ||
@@ -349,7 +383,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         return PTB_ERR_ARG;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    int accel = desc->accel;
+    int accel = d_blob ? (int)PTB_ACCEL_LBVH : desc->accel;
     // measured on random soups (scratch/soup_speed.py): the plane list in shared memory wins up to ~256 triangles
     // (2.0 vs 1.4 Gsamples/s at 64, 255 vs 207 Msamples/s at 256), the LBVH from ~400 on (119 vs 163 at 512)
     if (accel == PTB_ACCEL_AUTO) accel = desc->n_tri <= PTB_BRUTE_AUTO_TRI ? PTB_ACCEL_BRUTE : PTB_ACCEL_LBVH;
@@ -521,6 +555,35 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
     if (accel == PTB_ACCEL_LBVH) {
         const TriRec *ref_order = d.tri;      // the reference-order array stays allocated: source of both gathers
         double ms_all = 0.0, ms_occ = 0.0;
+        if (d_blob) {
+            // received hierarchy: check the header against this scene, then six device-to-device copies
+            BvhBlobHeader h;
+            if (cudaMemcpyAsync(&h, d_blob, sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+                ptb_scene_destroy(s); set_error("ptb_bvh_import: cannot read the buffer header"); return PTB_ERR_CUDA;
+            }
+            const bool want_occ = d.n_tri_obj >= 2;
+            const BvhBlobHeader w = bvh_blob_layout(n, d.n_tri_obj, want_occ, s->pad);
+            if (h.magic != BVH_BLOB_MAGIC || h.version != BVH_BLOB_VERSION || h.n_tri != n || h.n_tri_obj != d.n_tri_obj ||
+                h.has_occ != w.has_occ || h.pad != s->pad || h.total != w.total || blob_bytes < w.total) {
+                ptb_scene_destroy(s);
+                set_error("ptb_bvh_import: buffer does not belong to this scene (magic %08x version %u, %d/%d triangles, %llu bytes; expected %d/%d, %llu)",
+                          h.magic, h.version, h.n_tri, h.n_tri_obj, (unsigned long long)h.total, n, d.n_tri_obj, (unsigned long long)w.total);
+                return PTB_ERR_ARG;
+            }
+            void *sec[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+            for (int i = 0; i < (want_occ ? 6 : 3); ++i) {
+                const size_t bytes = (size_t)((i + 1 < 6 ? w.off[i + 1] : w.total) - w.off[i]);
+                if (cudaMalloc(&sec[i], std::max<size_t>(bytes, 256)) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+                s->allocs.push_back(sec[i]);
+                if (cudaMemcpyAsync(sec[i], (const char *)d_blob + w.off[i], bytes, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+                    ptb_scene_destroy(s); set_error("ptb_bvh_import: copy failed"); return PTB_ERR_CUDA;
+                }
+            }
+            d.nodes = (const BvhNode *)sec[0]; d.tri = (const TriRec *)sec[1]; d.tri_id = (const int *)sec[2];
+            d.nodes_occ = (const BvhNode *)sec[3]; d.tri_occ = (const TriRec *)sec[4]; d.tri_id_occ = (const int *)sec[5];
+            s->build_ms = 0.0;
+            s->n_nodes = n - 1;
+        } else {
         if ((rc = build_lbvh(s, n, no + 1, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, st))) { ptb_scene_destroy(s); return rc; }
         if (d.n_tri_obj >= 2) {
             if ((rc = build_lbvh(s, d.n_tri_obj, no, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, st))) { ptb_scene_destroy(s); return rc; }
@@ -529,6 +592,7 @@ extern "C" int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_sc
         }
         s->build_ms = ms_all + ms_occ;
         s->n_nodes = n - 1;
+        }
     }
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
     *out = s;
@@ -547,6 +611,35 @@ extern "C" int ptb_scene_info(const ptb_scene *s, int32_t *accel, int32_t *n_nod
     if (accel) *accel = s->d.accel;
     if (n_nodes) *n_nodes = s->n_nodes;
     if (build_ms) *build_ms = s->build_ms;
+    return PTB_OK;
+}
+
+extern "C" size_t ptb_bvh_export_bytes(const ptb_scene *s) {
+    if (!s || s->d.accel != PTB_ACCEL_LBVH || !s->d.nodes) return 0;
+    return (size_t)bvh_blob_layout(s->d.n_tri, s->d.n_tri_obj, s->d.nodes_occ != nullptr, s->pad).total;
+}
+
+extern "C" int ptb_bvh_export(const ptb_scene *s, void *d_blob, size_t blob_bytes, void *stream) {
+    if (!s || !d_blob) { set_error("ptb_bvh_export: null argument"); return PTB_ERR_ARG; }
+    if (s->d.accel != PTB_ACCEL_LBVH || !s->d.nodes) { set_error("ptb_bvh_export: the scene has no LBVH (shared-memory plane list)"); return PTB_ERR_UNSUPPORTED; }
+    const DScene &d = s->d;
+    const BvhBlobHeader h = bvh_blob_layout(d.n_tri, d.n_tri_obj, d.nodes_occ != nullptr, s->pad);
+    if (blob_bytes < h.total) { set_error("ptb_bvh_export: buffer of %zu bytes, %llu needed", blob_bytes, (unsigned long long)h.total); return PTB_ERR_NOMEM; }
+    cudaStream_t st = (cudaStream_t)stream;
+    // zero the header block and the alignment gaps so equal scenes export equal buffers
+    PTB_CUDA(cudaMemsetAsync(d_blob, 0, 256, st));
+    PTB_CUDA(cudaMemcpyAsync(d_blob, &h, sizeof(h), cudaMemcpyHostToDevice, st));
+    const void *src[6] = {d.nodes, d.tri, d.tri_id, d.nodes_occ, d.tri_occ, d.tri_id_occ};
+    const size_t no = h.has_occ ? (size_t)d.n_tri_obj : 0;
+    // a tree over n leaves has n - 1 nodes; the n-th slot of the node array is never written by the build
+    const size_t used[6] = {sizeof(BvhNode) * (size_t)(d.n_tri - 1), sizeof(TriRec) * (size_t)d.n_tri, 4 * (size_t)d.n_tri,
+                            no ? sizeof(BvhNode) * (no - 1) : 0, sizeof(TriRec) * no, 4 * no};
+    for (int i = 0; i < 6; ++i) {
+        const size_t span = (size_t)((i + 1 < 6 ? h.off[i + 1] : h.total) - h.off[i]);
+        if (used[i]) PTB_CUDA(cudaMemcpyAsync((char *)d_blob + h.off[i], src[i], used[i], cudaMemcpyDeviceToDevice, st));
+        if (span > used[i]) PTB_CUDA(cudaMemsetAsync((char *)d_blob + h.off[i] + used[i], 0, span - used[i], st));
+    }
+    PTB_CUDA(cudaStreamSynchronize(st));      // the header came from the stack
     return PTB_OK;
 }
 

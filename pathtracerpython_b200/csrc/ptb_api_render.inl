@@ -527,6 +527,20 @@ extern "C" int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, 
     return PTB_OK;
 }
 
+extern "C" int ptb_tonemap_scene(const float *d_accum, const int32_t *d_primary_tri, int32_t width, int32_t height,
+                                 double tonemapping, const double *background, uint8_t *d_rgb, void *stream) {
+    if (!d_accum || !d_rgb || width <= 0 || height <= 0 || !(tonemapping >= 0.0)) { set_error("ptb_tonemap_scene: bad argument"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int n = width * height;
+    const float bg[3] = {background ? (float)background[0] : 0.f, background ? (float)background[1] : 0.f, background ? (float)background[2] : 0.f};
+    { ProfScope ps_(PK_TONEMAP, st);
+    k_quantise_scene<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float4 *)d_accum, d_primary_tri, width, height,
+                                                                   (float)tonemapping, bg[0], bg[1], bg[2], d_rgb);
+    }
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
 extern "C" int ptb_scatter_accum(const ptb_pixels *px, const float *d_src, float *d_dst, void *stream) {
     int rc;
     if ((rc = check_pixels(px))) return rc;

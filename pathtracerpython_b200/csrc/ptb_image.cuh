@@ -56,6 +56,29 @@ __global__ void __launch_bounds__(256) k_quantise(const float4 *__restrict__ acc
     }
 }
 
+// Opt-in display transform from two scene keywords the reference parses and never reads (scene_reader.py:158-159
+// `background`, :167-168 `tonemapping`): v / (v + tm) on the per-pixel mean, clamped to [0, 1], * 255 truncated;
+// pixels whose primary ray left the scene show the background colour.  Same pixel mapping as k_quantise.
+__global__ void __launch_bounds__(256) k_quantise_scene(const float4 *__restrict__ accum, const int *__restrict__ primary_tri,
+                                                        int W, int H, float tm, float bgr, float bgg, float bgb,
+                                                        uint8_t *__restrict__ rgb) {
+    const int n = W * H;
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
+        const float4 a = accum[r];
+        const float c = a.w > 0.f ? a.w : 1.f;
+        const int ix = r / H, iy = r - ix * H;
+        uint8_t *o = rgb + ((size_t)(H - 1 - iy) * W + ix) * 3;
+        const bool miss = primary_tri && primary_tri[r] < 0;
+        const float v[3] = {a.x / c, a.y / c, a.z / c}, bg[3] = {bgr, bgg, bgb};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float q = miss ? bg[k] : (tm > 0.f ? v[k] / (v[k] + tm) : v[k]);
+            q = q > 0.f ? (q < 1.f ? q : 1.f) : 0.f;            // also sends NaN to 0
+            o[k] = (uint8_t)(int)(q * 255.f);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k_scatter_accum(PixelMap pm, const float4 *__restrict__ src, float4 *__restrict__ dst) {
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < pm.n; p += gridDim.x * blockDim.x)
         dst[pm.ray_index(p)] = src[p];

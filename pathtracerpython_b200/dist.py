@@ -36,6 +36,40 @@ def reduce_frame(full, dst=0, group=None):
     return full
 
 
+def replicate_renderer(scene, device, src=0, group=None, accel=0, make=None):
+    """One device scene per rank with the hierarchies built ONCE: rank `src` builds (ptb_scene_create), exports
+    both LBVHs into one device buffer (ptb_bvh_export) and broadcasts it (one collective, NCCL over NVLink);
+    every other rank imports it (ptb_bvh_import: device-to-device copies instead of sort / tree / refit).
+    Small scenes (shared-memory plane list, nothing to export: size 0 is broadcast) and single-process runs
+    build locally.  `make(scene, device, accel, bvh)` creates the renderer (tests inject a stand-in)."""
+    import torch
+    import torch.distributed as dist
+    if make is None:
+        from .render import Renderer
+        make = lambda sc, dev, acc, bvh: Renderer(sc, device=dev, accel=acc, bvh=bvh)
+    world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+    if world <= 1:
+        return make(scene, device, accel, None)
+    rank = dist.get_rank(group)
+    r, blob = None, None
+    size = torch.zeros(1, dtype=torch.int64, device=device)
+    if rank == src:
+        r = make(scene, device, accel, None)
+        try:
+            blob = r.export_bvh()
+            size[0] = blob.numel()
+        except Exception:           # no LBVH on this scene: everybody builds its own plane list
+            blob = None
+    dist.broadcast(size, src=src, group=group)
+    n = int(size.item())
+    if n == 0:
+        return r if r is not None else make(scene, device, accel, None)
+    if rank != src:
+        blob = torch.empty(n, dtype=torch.uint8, device=device)
+    dist.broadcast(blob, src=src, group=group)
+    return r if rank == src else make(scene, device, accel, blob)
+
+
 def render_step(renderer, spp, bounces, seed, width, height, rank=0, world=1, mode="tile", tile=None, full=None,
                 flags=0, tonemap=True):
     """One frame on this rank's share of the work; returns the u8 image tensor on rank 0 (else None)

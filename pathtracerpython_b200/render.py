@@ -29,7 +29,10 @@ def _torch():
 
 
 class Renderer:
-    def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None):
+    def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None, bvh=None):
+        """`bvh`: a uint8 device tensor from another Renderer's `export_bvh()` of the SAME scene (possibly
+        received from another rank, dist.replicate_renderer): the hierarchies are copied from it
+        (ptb_bvh_import) instead of being built."""
         torch = _torch()
         self.torch = torch
         self.scene = Scene(scene) if isinstance(scene, str) else scene
@@ -55,7 +58,13 @@ class Renderer:
         d.light_color[:] = [float(x) for x in f["light_color"][:3]]
         d.accel = accel
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().ptb_scene_create(C.byref(d), self._stream(), C.byref(self._handle)), "ptb_scene_create")
+            if bvh is None:
+                _lib.check(_lib.lib().ptb_scene_create(C.byref(d), self._stream(), C.byref(self._handle)), "ptb_scene_create")
+            else:
+                if bvh.dtype != torch.uint8 or bvh.device != self.device or not bvh.is_contiguous():
+                    raise PtbError("bvh must be a contiguous uint8 tensor on the renderer's device")
+                _lib.check(_lib.lib().ptb_bvh_import(C.byref(d), bvh.data_ptr(), bvh.numel(), self._stream(),
+                                                     C.byref(self._handle)), "ptb_bvh_import")
         self.n_tri = d.n_tri
 
     # ---- plumbing
@@ -201,11 +210,43 @@ class Renderer:
                        "ptb_tonemap")
         return rgb
 
+    def image_scene(self, accum_full, width=None, height=None, tonemapping=None, background=None, primary_tri=None):
+        """Opt-in alternative to `image`: the scene's `tonemapping` (v / (v + tm)) and `background` keywords, which the
+        reference parses and ignores (scene_reader.py:158-159, 167-168) -> uint8 tensor [H, W, 3].  `primary_tri`
+        (int32 per ray index, < 0 = miss) selects the background pixels; by default the primary rays are traced."""
+        torch = self.torch
+        W, H = int(width or self.width), int(height or self.height)
+        tm = self.flat.get("tonemapping") if tonemapping is None else tonemapping
+        bg = self.flat.get("background") if background is None else background
+        tm = 0.0 if tm is None else float(tm)
+        bg = (C.c_double * 3)(*[float(x) for x in (bg if bg is not None else (0.0, 0.0, 0.0))][:3])
+        if primary_tri is None:
+            primary_tri, _ = self.trace_primary(W, H)
+        rgb = torch.empty((H, W, 3), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_tonemap_scene(accum_full.data_ptr(), primary_tri.data_ptr(), W, H, tm, bg,
+                                                    rgb.data_ptr(), self._stream()), "ptb_tonemap_scene")
+        return rgb
+
     def scatter(self, px, accum_shard, accum_full):
         with self.torch.cuda.device(self.device):
             _lib.check(_lib.lib().ptb_scatter_accum(C.byref(px), accum_shard.data_ptr(), accum_full.data_ptr(), self._stream()),
                        "ptb_scatter_accum")
         return accum_full
+
+    def export_bvh(self, out=None):
+        """Both hierarchies of an LBVH scene as ONE uint8 device tensor (ptb_bvh_export) that `Renderer(scene,
+        bvh=...)` on any GPU turns back into a device scene without the build.  Raises for shared-memory scenes."""
+        torch = self.torch
+        L = _lib.lib()
+        nbytes = int(L.ptb_bvh_export_bytes(self._handle))
+        if nbytes == 0:
+            raise PtbError("export_bvh: the scene has no LBVH (small scenes live in shared memory)")
+        if out is None:
+            out = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(L.ptb_bvh_export(self._handle, out.data_ptr(), out.numel(), self._stream()), "ptb_bvh_export")
+        return out
 
     def info(self):
         """-> dict(accel, n_nodes, build_ms) of the device scene."""
@@ -223,16 +264,18 @@ class Renderer:
 
 
 def render(scene, n_rays=1, n_bounces=1, seed=None, width=None, height=None, device=None, precision=_lib.PREC_FP32,
-           flags=0, return_radiance=False):
+           flags=0, return_radiance=False, scene_tonemap=False):
     """Drop-in for the body of main() (main.py:165-293): scene (path or Scene) -> PIL.Image.
-    `seed` defaults to the scene's `seed` keyword (parsed but unused by the reference, A-Q19)."""
+    `seed` defaults to the scene's `seed` keyword (parsed but unused by the reference, A-Q19).
+    `scene_tonemap=True` (opt-in, not the reference's output) applies the scene's `tonemapping` / `background`
+    keywords (Renderer.image_scene) instead of make_image's min/max normalisation."""
     from PIL import Image
     r = Renderer(scene, device=device)
     try:
         if seed is None:
             seed = r.flat.get("seed") or 0
         accum, _ = r.trace_paths(n_rays, n_bounces, seed=seed, width=width, height=height, precision=precision, flags=flags)
-        rgb = r.image(accum, width, height)
+        rgb = r.image_scene(accum, width, height) if scene_tonemap else r.image(accum, width, height)
         im = Image.fromarray(rgb.cpu().numpy())
         if return_radiance:
             a = accum.cpu().numpy()

@@ -209,7 +209,7 @@ class Scene:
             "eye": np.asarray(self.eye, np.float64), "ortho": np.asarray(self.ortho, np.float64),
             "width": self.width, "height": self.height, "ambient": float(self.ambient),
             "light_color": np.asarray(self.light_color[:3], np.float64),
-            "npaths": self.npaths, "seed": self.seed,
+            "npaths": self.npaths, "seed": self.seed, "tonemapping": self.tonemapping, "background": self.background,
         }
 
 

@@ -30,6 +30,19 @@ def main():
         assert torch.allclose(ref, full_s, rtol=1e-5, atol=1e-5), "sample-sharded frame differs"
         assert torch.equal(r.image(ref, W, H), img_t)
         print(f"multi-GPU check ok on {world} ranks: tile sharding bitwise identical, sample sharding within 1e-5")
+    # hierarchy built once on rank 0 and broadcast (ptb_bvh_export / ptb_bvh_import) == built on every rank
+    from pathtracerpython_b200 import synth
+    big = synth.tessellate(ptb.Scene(ptb.CORNELL_SDL), 8)
+    rep = pdist.replicate_renderer(big, local, src=0, accel=ptb.ACCEL_LBVH)
+    own = ptb.Renderer(big, device=local, accel=ptb.ACCEL_LBVH)
+    assert rep.info()["build_ms"] == 0.0 or rank == 0
+    a_rep, _ = rep.trace_paths(2, 3, seed=4, width=96, height=96)
+    a_own, _ = own.trace_paths(2, 3, seed=4, width=96, height=96)
+    assert torch.equal(a_rep, a_own), f"rank {rank}: imported hierarchy renders differently"
+    small = pdist.replicate_renderer(ptb.CORNELL_SDL, local, src=0)      # nothing to export: every rank builds
+    assert small.info()["accel"] == "brute"
+    if rank == 0:
+        print("replicated hierarchy ok")
     dist.barrier()
     dist.destroy_process_group()
 

@@ -73,3 +73,42 @@ def test_partition_properties():
             px = _lib.Pixels(W, H, g, G, tile, 0, None)
             assert _lib.lib().ptb_pixel_count(ctypes.byref(px)) == len(parts[g])
     assert [pdist.sample_range(10, r, 4) for r in range(4)] == [(0, 2), (2, 5), (5, 7), (7, 10)]
+
+
+class _FakeRenderer:
+    """Stand-in for Renderer in the CPU test of dist.replicate_renderer: 'builds' a blob from the scene."""
+    def __init__(self, scene, bvh):
+        self.scene, self.imported = scene, bvh is not None
+        self.blob = bvh if bvh is not None else (torch.arange(scene["n"], dtype=torch.int64) * 7 % 251).to(torch.uint8)
+
+    def export_bvh(self):
+        if self.scene["n"] == 0:
+            raise RuntimeError("no LBVH")
+        return self.blob
+
+
+def _replicate_worker(rank, world, port, n, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    made = []
+
+    def make(scene, device, accel, bvh):
+        made.append(bvh is not None)
+        return _FakeRenderer(scene, bvh)
+    r = pdist.replicate_renderer({"n": n}, "cpu", src=0, make=make)
+    torch.save({"imported": r.imported, "made": made, "blob": r.blob}, f"{out}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_replicate_renderer_protocol_gloo(tmp_path):
+    """rank 0 builds and broadcasts, rank 1 imports the same bytes; a scene with nothing to export is built everywhere."""
+    out = str(tmp_path / "rep")
+    mp.spawn(_replicate_worker, args=(2, _free_port(), 1000, out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert r0["made"] == [False] and not r0["imported"]
+    assert r1["made"] == [True] and r1["imported"] and torch.equal(r0["blob"], r1["blob"])
+    mp.spawn(_replicate_worker, args=(2, _free_port(), 0, out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert r0["made"] == [False] and r1["made"] == [False] and not r1["imported"]

@@ -251,3 +251,38 @@ def test_lbvh_duplicate_triangles_resolve_ties_like_the_reference(cornell):
     n_in = np.array([(np.asarray(flat["tri_obj"]) == k).sum() for k in range(int(obj.max()) + 1)])
     keep = obj < len(dup.objects)
     assert ((hit[keep] - first[obj[keep]]) < n_in[obj[keep]] // 2).all()
+
+
+def test_bvh_export_import_is_bitwise_identical(cornell, tess8):
+    """ptb_bvh_export -> ptb_bvh_import (replicate instead of rebuild): an imported scene traces
+    and renders exactly what the built one does; a buffer of another scene, a truncated buffer and a small
+    (shared-memory) scene are refused."""
+    import torch
+    built = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
+    blob = built.export_bvh()
+    assert blob.dtype == torch.uint8 and blob.numel() % 256 == 0
+    assert torch.equal(blob, built.export_bvh())                       # deterministic, gaps zeroed
+    again = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
+    assert torch.equal(blob, again.export_bvh())                       # the build itself is deterministic
+    again.close()
+    imp = ptb.Renderer(tess8, device=0, bvh=blob.clone())
+    assert imp.info()["accel"] == "lbvh" and imp.info()["build_ms"] == 0.0 and imp.info()["n_nodes"] == built.info()["n_nodes"]
+    t0, d0 = built.trace_primary(128, 128)
+    t1, d1 = imp.trace_primary(128, 128)
+    assert torch.equal(t0, t1) and torch.equal(d0, d1)
+    a0, r0 = built.trace_paths(3, 4, seed=21, width=96, height=64, records=True)
+    a1, r1 = imp.trace_paths(3, 4, seed=21, width=96, height=64, records=True)
+    assert torch.equal(a0, a1)
+    for k in r0:
+        assert torch.equal(r0[k], r1[k]), k
+    assert torch.equal(imp.export_bvh(), blob)                         # round trip
+    # wrong scene / truncated buffer / no LBVH
+    other = synth.tessellate(cornell, 5)
+    with pytest.raises(ptb.PtbError, match="does not belong"):
+        ptb.Renderer(other, device=0, bvh=blob)
+    with pytest.raises(ptb.PtbError):
+        ptb.Renderer(tess8, device=0, bvh=blob[:blob.numel() // 2].clone())
+    small = ptb.Renderer(cornell, device=0)
+    with pytest.raises(ptb.PtbError, match="no LBVH"):
+        small.export_bvh()
+    small.close(); built.close(); imp.close()

@@ -247,6 +247,34 @@ def test_aovs_and_cli(tmp_path, flat):
     assert Image.open(out).size == (40, 40)
 
 
+def test_scene_keywords_opt_in(tmp_path, rnd, flat):
+    """`tonemapping`, `background`, `output` (scene_reader.py:158-159, 167-168, 184-185) are parsed and ignored by the
+    reference; here they are opt-in: ptb_tonemap_scene against its own formula, the CLI writing the scene's .pnm."""
+    import shutil
+    accum, _ = rnd.trace_paths(4, 2, seed=3)
+    tri, _ = rnd.trace_primary()
+    a = accum.cpu().numpy().astype(np.float32)
+    mean = a[:, :3] / np.maximum(a[:, 3:4], np.float32(1))
+    bg = [0.25, 0.5, 0.75]
+    got = rnd.image_scene(accum, tonemapping=1.0, background=bg).cpu().numpy()
+    v = np.clip(mean / (mean + np.float32(1.0)), 0, 1)
+    v = np.where((tri.cpu().numpy() < 0)[:, None], np.asarray(bg, np.float32), v)
+    want = (v * np.float32(255)).astype(np.uint8).reshape(40, 40, 3)          # [ix, iy] -> row H-1-iy, column ix
+    want = want.transpose(1, 0, 2)[::-1]
+    assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and (got != want).mean() < 1e-3
+    assert np.array_equal(rnd.image_scene(accum).cpu().numpy(),               # defaults = the scene's own keywords
+                          rnd.image_scene(accum, tonemapping=rnd.flat["tonemapping"], background=rnd.flat["background"]).cpu().numpy())
+    # CLI: --use-output writes the scene's `output cornell.pnm` (binary PPM) next to the scene file
+    d = tmp_path / "sc"
+    shutil.copytree(os.path.dirname(ptb.CORNELL_SDL), str(d))
+    from pathtracerpython_b200.__main__ import main
+    assert main([str(d / "cornellroom.sdl"), "-r", "2", "-b", "2", "--use-output", "--scene-tonemap", "--use-npaths"]) == 0
+    raw = open(str(d / "cornell.pnm"), "rb").read()
+    assert raw[:2] == b"P6" and len(raw) > 40 * 40 * 3
+    from PIL import Image
+    assert Image.open(str(d / "cornell.pnm")).size == (40, 40)
+
+
 def test_errors_are_loud(rnd):
     with pytest.raises(ptb.PtbError):
         rnd.trace_paths(1, 1, shard=5, n_shards=2)
