@@ -210,12 +210,17 @@ def run_ours(a):
     scene.flatten(pin=True)
 
     def e2e_step():
+        t0 = time.perf_counter()
         rr = ptb.Renderer(scene, device=local)
+        t1 = time.perf_counter()
         img = step(rr)
         if img is not None:
             host_img.copy_(img, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        t2 = time.perf_counter()
         rr.close()
+        if os.environ.get("PTB_TIMING"):
+            print(f"[bench e2e] create {1e3 * (t1 - t0):.1f} ms, frame + image {1e3 * (t2 - t1):.1f} ms, close {1e3 * (time.perf_counter() - t2):.1f} ms", file=sys.stderr)
 
     e2e_step()
     ms_e2e = timed(e2e_step, a.steps)

@@ -127,6 +127,10 @@ int ptb_version(void);
  * scene (main.py:199-201): uploads the flattened scene and builds the acceleration structure. */
 int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out);
 int ptb_scene_destroy(ptb_scene *scene);
+/* Scene memory is taken from the device's stream-ordered pool and returns to it on ptb_scene_destroy, so that creating a
+ * scene per frame does not pay the driver's allocator each time; ptb_pool_trim hands the pool's unused memory back to
+ * the driver (synchronises the device). */
+int ptb_pool_trim(void);
 int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, double *build_ms);
 
 /* Replicating a built scene to other GPUs instead of rebuilding it (the reference pickles the whole scene into

@@ -14,7 +14,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
-           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene"]
+           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim"]
 
 
 class PtbError(RuntimeError):

@@ -4,6 +4,7 @@
 #include <stdarg.h>
 
 #include <algorithm>
+#include <chrono>
 #include <vector>
 
 #include "ptb_image.cuh"
@@ -83,6 +84,34 @@ extern "C" int ptb_profile_read(double *ms, uint64_t *launches) {
     return PTB_OK;
 }
 
+// Scene memory comes from the device's stream-ordered pool (cudaMallocAsync) with the release threshold lifted, so
+// creating and destroying scenes (a scene per frame, bench.py's end-to-end step) recycles pool memory instead of going
+// to the driver's allocator: cudaFree synchronises the device and was measured at 4-240 ms per scene.
+static int pool_ready_for = -1;
+static cudaError_t scene_malloc(void **p, size_t bytes, cudaStream_t st) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (pool_ready_for != dev) {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        pool_ready_for = dev;
+    }
+    return cudaMallocAsync(p, std::max<size_t>(bytes, 256), st);
+}
+// ptb_pool_trim (include/ptb.h): hand the pool's unused memory back to the driver
+extern "C" int ptb_pool_trim(void) {
+    int dev = 0;
+    cudaMemPool_t pool;
+    PTB_CUDA(cudaGetDevice(&dev));
+    PTB_CUDA(cudaDeviceSynchronize());
+    PTB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    PTB_CUDA(cudaMemPoolTrimTo(pool, 0));
+    return PTB_OK;
+}
+
 struct ptb_scene {
     DScene d;                       // device view handed to kernels by value
     std::vector<void *> allocs;     // device allocations owned by the handle
@@ -100,7 +129,7 @@ struct ptb_scene {
 template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, const T **out, cudaStream_t st) {
     void *p = nullptr;
     size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
-    PTB_CUDA(cudaMalloc(&p, bytes));
+    PTB_CUDA(scene_malloc(&p, bytes, st));
     s->allocs.push_back(p);
     if (!h.empty()) PTB_CUDA(cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
     *out = (const T *)p;
@@ -109,7 +138,7 @@ template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, c
 
 template <typename T> static int upload_raw(ptb_scene *s, const T *src, size_t count, const T **out, cudaStream_t st) {
     void *p = nullptr;
-    PTB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    PTB_CUDA(scene_malloc(&p, std::max<size_t>(count, 1) * sizeof(T), st));
     s->allocs.push_back(p);
     if (count) PTB_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
     *out = (const T *)p;
@@ -219,8 +248,13 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
 // box) and the radix tree is built over that 64-bit key, so the top levels separate whole meshes (the reference's
 // scenes are lists of `object file.obj` meshes: walls, blocks) and every mesh gets a subtree with tight boxes - flat
 // for a wall.  n_objs = number of object ids among the n triangles.
+static size_t lbvh_arena_bytes(int n, int n_objs) {      // upper bound of what build_lbvh carves (sum of its temporaries)
+    const size_t nn = (size_t)n, tiles = (nn + PS_TILE - 1) / PS_TILE;
+    return nn * (2 * sizeof(Aabb) + sizeof(float4) + sizeof(int2) + 4 * 9 + 8) + 4 * 256 * tiles + (size_t)n_objs * 52 + 64 * 256;
+}
+
 static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
-                      const int **ids_out, double *ms_out, cudaStream_t st) {
+                      const int **ids_out, double *ms_out, void *arena, size_t arena_bytes, cudaStream_t st) {
     DScene &d = s->d;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -229,28 +263,33 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
     int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
     unsigned *ghist = nullptr, *flags = nullptr, *totals = nullptr, *d_n = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
     unsigned *obj_box = nullptr, *morton_orig = nullptr; unsigned long long *key64 = nullptr; float *obj_lo = nullptr, *obj_inv = nullptr; int *rank = nullptr;
-    std::vector<void *> tmp;
-    auto alloc = [&](void **p, size_t bytes, bool keep) -> int {
-        PTB_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));
-        (keep ? s->allocs : tmp).push_back(*p);
-        return PTB_OK;
-    };
-    int rc;
-    if ((rc = alloc((void **)&tri_box, sizeof(Aabb) * n, false)) || (rc = alloc((void **)&node_box, sizeof(Aabb) * n, false)) ||
-        (rc = alloc((void **)&centroid, sizeof(float4) * n, false)) || (rc = alloc((void **)&scene_box, 64, false)) ||
-        (rc = alloc((void **)&keys[0], 4 * (size_t)n, false)) || (rc = alloc((void **)&keys[1], 4 * (size_t)n, false)) ||
-        (rc = alloc((void **)&vals[0], 4 * (size_t)n, false)) || (rc = alloc((void **)&vals[1], 4 * (size_t)n, true)) ||
-        (rc = alloc((void **)&parent_inner, 4 * (size_t)n, false)) || (rc = alloc((void **)&parent_leaf, 4 * (size_t)n, false)) ||
-        (rc = alloc((void **)&node_minref, 4 * (size_t)n, false)) || (rc = alloc((void **)&child, sizeof(int2) * n, false)) ||
-        (rc = alloc((void **)&ghist, 4 * (size_t)256 * n_tiles, false)) || (rc = alloc((void **)&totals, 4 * 256, false)) ||
-        (rc = alloc((void **)&d_n, 16, false)) || (rc = alloc((void **)&flags, 4 * (size_t)n, false)) ||
-        (rc = alloc((void **)&obj_box, 24 * (size_t)n_objs, false)) || (rc = alloc((void **)&morton_orig, 4 * (size_t)n, false)) ||
-        (rc = alloc((void **)&key64, 8 * (size_t)n, false)) || (rc = alloc((void **)&obj_lo, 12 * (size_t)n_objs, false)) ||
-        (rc = alloc((void **)&obj_inv, 12 * (size_t)n_objs, false)) || (rc = alloc((void **)&rank, 4 * (size_t)n_objs, false)) ||
-        (rc = alloc((void **)&nodes, sizeof(BvhNode) * (size_t)n, true)) || (rc = alloc((void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true))) {
-        for (void *p : tmp) cudaFree(p);
-        return rc;
+    // temporaries are carved out of ONE arena owned by the caller (both trees of a scene share it): twenty-odd cudaMalloc /
+    // cudaFree pairs per tree cost ten times the 1.6 ms the build kernels take (cudaFree synchronises the device)
+    struct Want { void **p; size_t bytes; bool keep; };
+    const Want wants[] = {
+        {(void **)&tri_box, sizeof(Aabb) * (size_t)n, false}, {(void **)&node_box, sizeof(Aabb) * (size_t)n, false},
+        {(void **)&centroid, sizeof(float4) * (size_t)n, false}, {(void **)&scene_box, 64, false},
+        {(void **)&keys[0], 4 * (size_t)n, false}, {(void **)&keys[1], 4 * (size_t)n, false},
+        {(void **)&vals[0], 4 * (size_t)n, false}, {(void **)&vals[1], 4 * (size_t)n, true},
+        {(void **)&parent_inner, 4 * (size_t)n, false}, {(void **)&parent_leaf, 4 * (size_t)n, false},
+        {(void **)&node_minref, 4 * (size_t)n, false}, {(void **)&child, sizeof(int2) * (size_t)n, false},
+        {(void **)&ghist, 4 * (size_t)256 * n_tiles, false}, {(void **)&totals, 4 * 256, false},
+        {(void **)&d_n, 16, false}, {(void **)&flags, 4 * (size_t)n, false},
+        {(void **)&obj_box, 24 * (size_t)n_objs, false}, {(void **)&morton_orig, 4 * (size_t)n, false},
+        {(void **)&key64, 8 * (size_t)n, false}, {(void **)&obj_lo, 12 * (size_t)n_objs, false},
+        {(void **)&obj_inv, 12 * (size_t)n_objs, false}, {(void **)&rank, 4 * (size_t)n_objs, false},
+        {(void **)&nodes, sizeof(BvhNode) * (size_t)n, true}, {(void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true}};
+    size_t at = 0;
+    for (const Want &w : wants) {
+        if (w.keep) {
+            PTB_CUDA(scene_malloc(w.p, w.bytes, st));
+            s->allocs.push_back(*w.p);
+        } else {
+            *w.p = (char *)arena + at;
+            at += (std::max<size_t>(w.bytes, 16) + 255) & ~(size_t)255;
+        }
     }
+    if (at > arena_bytes) { set_error("LBVH build: arena of %zu bytes, %zu needed", arena_bytes, at); return PTB_ERR_NOMEM; }
     const unsigned h_n = (unsigned)n;
     cudaMemcpyAsync(d_n, &h_n, sizeof(unsigned), cudaMemcpyHostToDevice, st);
     cudaEventRecord(e0, st);
@@ -266,7 +305,7 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
         std::vector<unsigned> h_box((size_t)n_objs * 6 + 6);
         cudaMemcpyAsync(h_box.data(), obj_box, 24 * (size_t)n_objs, cudaMemcpyDeviceToHost, st);
         cudaMemcpyAsync(h_box.data() + (size_t)n_objs * 6, scene_box, 24, cudaMemcpyDeviceToHost, st);
-        if (cudaStreamSynchronize(st) != cudaSuccess) { for (void *p : tmp) cudaFree(p); set_error("LBVH build: bounds pass failed"); return PTB_ERR_CUDA; }
+        if (cudaStreamSynchronize(st) != cudaSuccess) { set_error("LBVH build: bounds pass failed"); return PTB_ERR_CUDA; }
         auto unorder = [](unsigned o) { unsigned b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; float f; memcpy(&f, &b, 4); return f; };
         const bool flat = getenv("PTB_BVH_FLAT") != nullptr;
         float slo[3], shi[3];
@@ -327,7 +366,6 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    for (void *p : tmp) cudaFree(p);
     if (err != cudaSuccess) { set_error("LBVH build failed: %s", cudaGetErrorString(err)); return PTB_ERR_CUDA; }
     *nodes_out = nodes;
     *tri_out = tri_sorted;    // leaf order
@@ -374,7 +412,19 @@ extern "C" int ptb_bvh_import(const ptb_scene_desc *desc, const void *d_blob, si
     return scene_create_impl(desc, d_blob, blob_bytes, stream, out);
 }
 
+struct PhaseTimer {     // PTB_TIMING=1: host wall-clock of the phases of scene creation on stderr
+    bool on; std::chrono::steady_clock::time_point t0;
+    PhaseTimer() : on(getenv("PTB_TIMING") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char *what) {
+        if (!on) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[ptb timing] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, size_t blob_bytes, void *stream, ptb_scene **out) {
+    PhaseTimer pt_;
     if (!desc || !out) { set_error("ptb_scene_create: null argument"); return PTB_ERR_ARG; }
     if (desc->n_tri <= 0 || desc->n_tri_obj < 0 || desc->n_tri_obj > desc->n_tri || desc->n_obj <= 0 ||
         desc->n_light_tri != desc->n_tri - desc->n_tri_obj || desc->n_light_tri <= 0 || !desc->verts ||
@@ -413,12 +463,12 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         const int blocks = grid_for((size_t)n * 3, 256, 4);
         double *d_ext = nullptr;
         std::vector<double> h_ext((size_t)blocks * 8);
-        if (cudaMalloc(&d_ext, h_ext.size() * sizeof(double)) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        if (scene_malloc((void **)&d_ext, h_ext.size() * sizeof(double), st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
         k_scene_extent<<<blocks, 256, 0, st>>>(d.verts64, (size_t)n * 3, d.tri_obj, n, no, d_ext);
         ++g_launches;
         cudaMemcpyAsync(h_ext.data(), d_ext, h_ext.size() * sizeof(double), cudaMemcpyDeviceToHost, st);
         cudaError_t e = cudaStreamSynchronize(st);
-        cudaFree(d_ext);
+        cudaFreeAsync(d_ext, st);
         if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("scene extent: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
         bool bad_obj = false;
         for (int b = 0; b < blocks; ++b) {
@@ -433,15 +483,16 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         for (size_t i = 0; i < (size_t)n * 3; ++i)
             for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], desc->verts[3 * i + k]); bhi[k] = std::max(bhi[k], desc->verts[3 * i + k]); }
     }
+    pt_.mark("upload + extent");
     for (int i = 0; i < 3; ++i) scale = std::max(scale, fabs(desc->eye[i]));
     s->dt_scale = (float)(32.0 * 5.9604644775390625e-08 * scale);
     for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)blo[k]; d.bb_inv[k] = (float)(256.0 / std::max(bhi[k] - blo[k], 1e-30)); }
 
     if (dev_records) {
         TriRec *d_tri = nullptr; float4 *d_sn = nullptr;
-        if (cudaMalloc((void **)&d_tri, sizeof(TriRec) * (size_t)n) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        if (scene_malloc((void **)&d_tri, sizeof(TriRec) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
         s->allocs.push_back(d_tri);
-        if (cudaMalloc((void **)&d_sn, sizeof(float4) * (size_t)n) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        if (scene_malloc((void **)&d_sn, sizeof(float4) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
         s->allocs.push_back(d_sn);
         k_make_records<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, d.normals64, d.tri_obj, n, scale, d_tri, d_sn);
         ++g_launches;
@@ -457,6 +508,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             ids[i] = i;
         }
     }
+    pt_.mark("records");
     const int32_t *tobj = desc->tri_obj;
     std::vector<double> mat64((size_t)(no + 1) * 8, 0.0);
     std::copy(desc->mat, desc->mat + (size_t)no * 8, mat64.begin());
@@ -517,6 +569,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         lobe_thr[k] = (int)first_m([&](unsigned m) { return !(0.0 + ((kd + ks) - 0.0) * ((double)m * 5.9604644775390625e-08) <= kd); });
         if (ne >= 0.0 && ne <= 64.0 && ne == floor(ne)) pow_int[k] = (int)ne;
     }
+    pt_.mark("light tables (host)");
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<int> obj_first(no + 2, n);
     for (int i = n - 1; i >= 0; --i) obj_first[tobj[i]] = i;
@@ -538,6 +591,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         ptb_scene_destroy(s);
         return rc;
     }
+    pt_.mark("obj_first + small uploads");
     d.n_tri = n; d.n_tri_obj = desc->n_tri_obj; d.n_obj = no; d.n_light_tri = desc->n_light_tri;
     d.accel = accel;
     for (int i = 0; i < 3; ++i) { d.eye[i] = desc->eye[i]; d.light_color[i] = desc->light_color[i]; }
@@ -573,7 +627,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             void *sec[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
             for (int i = 0; i < (want_occ ? 6 : 3); ++i) {
                 const size_t bytes = (size_t)((i + 1 < 6 ? w.off[i + 1] : w.total) - w.off[i]);
-                if (cudaMalloc(&sec[i], std::max<size_t>(bytes, 256)) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+                if (scene_malloc(&sec[i], bytes, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
                 s->allocs.push_back(sec[i]);
                 if (cudaMemcpyAsync(sec[i], (const char *)d_blob + w.off[i], bytes, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
                     ptb_scene_destroy(s); set_error("ptb_bvh_import: copy failed"); return PTB_ERR_CUDA;
@@ -584,16 +638,22 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             s->build_ms = 0.0;
             s->n_nodes = n - 1;
         } else {
-        if ((rc = build_lbvh(s, n, no + 1, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, st))) { ptb_scene_destroy(s); return rc; }
+        void *arena = nullptr;
+        const size_t arena_bytes = lbvh_arena_bytes(n, no + 1);
+        if (scene_malloc(&arena, arena_bytes, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory (LBVH build arena, %zu bytes)", arena_bytes); return PTB_ERR_CUDA; }
+        if ((rc = build_lbvh(s, n, no + 1, ref_order, &d.nodes, &d.tri, &d.tri_id, &ms_all, arena, arena_bytes, st))) { cudaFreeAsync(arena, st); ptb_scene_destroy(s); return rc; }
         if (d.n_tri_obj >= 2) {
-            if ((rc = build_lbvh(s, d.n_tri_obj, no, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, st))) { ptb_scene_destroy(s); return rc; }
-        } else {                              // degenerate occlusion set: fall back to the full tree + min-ref pruning
+            if ((rc = build_lbvh(s, d.n_tri_obj, no, ref_order, &d.nodes_occ, &d.tri_occ, &d.tri_id_occ, &ms_occ, arena, arena_bytes, st))) { cudaFreeAsync(arena, st); ptb_scene_destroy(s); return rc; }
+            cudaFreeAsync(arena, st);
+        } else {
+            cudaFreeAsync(arena, st);                              // degenerate occlusion set: fall back to the full tree + min-ref pruning
             d.nodes_occ = nullptr; d.tri_occ = nullptr; d.tri_id_occ = nullptr;
         }
         s->build_ms = ms_all + ms_occ;
         s->n_nodes = n - 1;
         }
     }
+    pt_.mark("hierarchies");
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
     *out = s;
     return PTB_OK;
@@ -601,7 +661,13 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
 
 extern "C" int ptb_scene_destroy(ptb_scene *s) {
     if (!s) return PTB_OK;
-    for (void *p : s->allocs) cudaFree(p);
+    // every stream that used the scene must be done with it before its memory goes back to the pool
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (cur != s->device) cudaSetDevice(s->device);
+    cudaDeviceSynchronize();
+    for (void *p : s->allocs) cudaFreeAsync(p, 0);
+    if (cur != s->device) cudaSetDevice(cur);
     delete s;
     return PTB_OK;
 }

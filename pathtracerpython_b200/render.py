@@ -28,6 +28,26 @@ def _torch():
     return torch
 
 
+# One workspace per device, shared by every Renderer of the process: the wavefront state of a batch is tens of GB, and
+# allocating it again for each new Renderer (a scene per frame in an animation, bench.py's end-to-end step) costs more
+# than building the scene.  Keyed by (device, CUDA stream): calls on one stream are ordered, so they can share it; a second
+# stream gets its own.  It only grows; release_workspace() hands it back.
+_WORKSPACES = {}
+
+
+def release_workspace(device=None):
+    """Free the shared wavefront workspace of `device` (all devices when None)."""
+    for k in [k for k in _WORKSPACES if device is None or k[0] == _dev_key(device)]:
+        del _WORKSPACES[k]
+    _lib.check(_lib.lib().ptb_pool_trim(), "ptb_pool_trim")      # and the scene pool's unused memory (current device)
+
+
+def _dev_key(device):
+    import torch
+    d = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
 class Renderer:
     def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None, bvh=None):
         """`bvh`: a uint8 device tensor from another Renderer's `export_bvh()` of the SAME scene (possibly
@@ -100,10 +120,14 @@ class Renderer:
         return int(_lib.lib().ptb_pixel_count(C.byref(px)))
 
     def workspace(self, nbytes):
-        if self._ws is None or self._ws.numel() < nbytes:
-            self._ws = None
-            self._ws = self.torch.empty(int(nbytes), dtype=self.torch.uint8, device=self.device)
-        return self._ws
+        key = (_dev_key(self.device), self.torch.cuda.current_stream(self.device).cuda_stream)
+        ws = _WORKSPACES.get(key)
+        if ws is None or ws.numel() < nbytes:
+            _WORKSPACES.pop(key, None)
+            ws = None
+            ws = _WORKSPACES[key] = self.torch.empty(int(nbytes), dtype=self.torch.uint8, device=self.device)
+        self._ws = ws
+        return ws
 
     # ---- parity seam 1
     def trace_primary(self, width=None, height=None, pixel_list=None, precision=_lib.PREC_FP32, flags=0):
@@ -186,7 +210,10 @@ class Renderer:
             ws_bytes = self.workspace_bytes
         else:
             # default: as many samples per batch as fit in ~1/4 of free memory, at most all of them
+            # (what the shared workspace already holds counts as free, so the batch size does not drift from call to call)
             free, _ = torch.cuda.mem_get_info(self.device)
+            held = _WORKSPACES.get((_dev_key(self.device), torch.cuda.current_stream(self.device).cuda_stream))
+            free += held.numel() if held is not None else 0
             one = L.ptb_trace_paths_workspace(C.byref(p), 1)
             spb = max(1, min(n_rays, int((free // 4) // max(one, 1)), (2 ** 31 - 1) // max(npix, 1)))
             if samples_per_batch:
@@ -194,7 +221,8 @@ class Renderer:
             ws_bytes = L.ptb_trace_paths_workspace(C.byref(p), spb)
         ws = self.workspace(ws_bytes)
         with torch.cuda.device(self.device):
-            _lib.check(L.ptb_trace_paths(self._handle, C.byref(p), ws.data_ptr(), ws.numel(), accum.data_ptr(),
+            # the size asked for, not the (shared, possibly larger) tensor's: a caller-imposed budget stays a budget
+            _lib.check(L.ptb_trace_paths(self._handle, C.byref(p), ws.data_ptr(), int(ws_bytes), accum.data_ptr(),
                                          C.byref(rec) if rec is not None else None, self._stream()), "ptb_trace_paths")
         return accum, rec_t
 
