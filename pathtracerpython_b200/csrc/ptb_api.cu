@@ -457,58 +457,30 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     std::vector<TriRec> tri;
     std::vector<float4> sn;
     std::vector<int> ids;
-    if (dev_records) {
+    int ext_blocks = 0;
+    double *d_ext = nullptr;
+    // page-locked landing buffer for the extent pass: a device-to-host copy into pageable memory would block the host
+    // until the uploads ahead of it in the stream are done, and the host has tables to compute meanwhile
+    static double *h_ext_pinned = nullptr; static size_t h_ext_cap = 0;
+    struct ExtView { double *p; size_t n; double *data() const { return p; } size_t size() const { return n; } void resize(size_t) {} } h_ext = {nullptr, 0};
+    if (dev_records) {      // issue the big uploads and the extent pass; the host tables below are computed while they run
         if ((rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st)) ||
             (rc = upload_raw(s, desc->tri_obj, (size_t)n, &d.tri_obj, st))) { ptb_scene_destroy(s); return rc; }
-        const int blocks = grid_for((size_t)n * 3, 256, 4);
-        double *d_ext = nullptr;
-        std::vector<double> h_ext((size_t)blocks * 8);
+        ext_blocks = grid_for((size_t)n * 3, 256, 4);
+        h_ext.n = (size_t)ext_blocks * 8;
+        if (h_ext_cap < h_ext.n) {
+            if (h_ext_pinned) cudaFreeHost(h_ext_pinned);
+            h_ext_pinned = nullptr; h_ext_cap = 0;
+            if (cudaMallocHost((void **)&h_ext_pinned, h_ext.n * sizeof(double)) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of page-locked host memory"); return PTB_ERR_CUDA; }
+            h_ext_cap = h_ext.n;
+        }
+        h_ext.p = h_ext_pinned;
         if (scene_malloc((void **)&d_ext, h_ext.size() * sizeof(double), st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
-        k_scene_extent<<<blocks, 256, 0, st>>>(d.verts64, (size_t)n * 3, d.tri_obj, n, no, d_ext);
+        k_scene_extent<<<ext_blocks, 256, 0, st>>>(d.verts64, (size_t)n * 3, d.tri_obj, n, no, d_ext);
         ++g_launches;
         cudaMemcpyAsync(h_ext.data(), d_ext, h_ext.size() * sizeof(double), cudaMemcpyDeviceToHost, st);
-        cudaError_t e = cudaStreamSynchronize(st);
-        cudaFreeAsync(d_ext, st);
-        if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("scene extent: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
-        bool bad_obj = false;
-        for (int b = 0; b < blocks; ++b) {
-            const double *x = h_ext.data() + 8 * (size_t)b;
-            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], x[k]); bhi[k] = std::max(bhi[k], x[3 + k]); }
-            scale = std::max(scale, x[6]);
-            bad_obj = bad_obj || x[7] != 0.0;
-        }
-        if (bad_obj) { ptb_scene_destroy(s); set_error("tri_obj out of range"); return PTB_ERR_ARG; }
-    } else {
-        for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
-        for (size_t i = 0; i < (size_t)n * 3; ++i)
-            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], desc->verts[3 * i + k]); bhi[k] = std::max(bhi[k], desc->verts[3 * i + k]); }
     }
-    pt_.mark("upload + extent");
-    for (int i = 0; i < 3; ++i) scale = std::max(scale, fabs(desc->eye[i]));
-    s->dt_scale = (float)(32.0 * 5.9604644775390625e-08 * scale);
-    for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)blo[k]; d.bb_inv[k] = (float)(256.0 / std::max(bhi[k] - blo[k], 1e-30)); }
-
-    if (dev_records) {
-        TriRec *d_tri = nullptr; float4 *d_sn = nullptr;
-        if (scene_malloc((void **)&d_tri, sizeof(TriRec) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
-        s->allocs.push_back(d_tri);
-        if (scene_malloc((void **)&d_sn, sizeof(float4) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
-        s->allocs.push_back(d_sn);
-        k_make_records<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, d.normals64, d.tri_obj, n, scale, d_tri, d_sn);
-        ++g_launches;
-        d.tri = d_tri; d.tri_sn = d_sn; d.tri_id = nullptr;
-    } else {
-        tri.resize(n); sn.resize(n); ids.resize(n);
-        for (int i = 0; i < n; ++i) {
-            if (desc->tri_obj[i] < 0 || desc->tri_obj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
-            tri[i] = make_trirec(desc->verts + 9 * (size_t)i, desc->tri_obj[i], scale);
-            tri[i].q3.w = bits_f(i);                     // reference index travels with the record (LBVH leaf order)
-            const double *nn = desc->normals + 3 * (size_t)i;
-            sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(desc->tri_obj[i]));
-            ids[i] = i;
-        }
-    }
-    pt_.mark("records");
+    pt_.mark("uploads issued");
     const int32_t *tobj = desc->tri_obj;
     std::vector<double> mat64((size_t)(no + 1) * 8, 0.0);
     std::copy(desc->mat, desc->mat + (size_t)no * 8, mat64.begin());
@@ -569,11 +541,54 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         lobe_thr[k] = (int)first_m([&](unsigned m) { return !(0.0 + ((kd + ks) - 0.0) * ((double)m * 5.9604644775390625e-08) <= kd); });
         if (ne >= 0.0 && ne <= 64.0 && ne == floor(ne)) pow_int[k] = (int)ne;
     }
-    pt_.mark("light tables (host)");
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<int> obj_first(no + 2, n);
-    for (int i = n - 1; i >= 0; --i) obj_first[tobj[i]] = i;
+    for (int i = n - 1; i >= 0; --i) { const int o = tobj[i]; if ((unsigned)o <= (unsigned)no) obj_first[o] = i; }   // range is checked below
     for (int k = no; k >= 0; --k) if (obj_first[k] == n && k + 1 <= no + 1) obj_first[k] = obj_first[k + 1];
+    pt_.mark("light tables, obj_first (host)");
+    if (dev_records) {
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFreeAsync(d_ext, st);
+        if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("scene extent: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
+        bool bad_obj = false;
+        for (int b = 0; b < ext_blocks; ++b) {
+            const double *x = h_ext.data() + 8 * (size_t)b;
+            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], x[k]); bhi[k] = std::max(bhi[k], x[3 + k]); }
+            scale = std::max(scale, x[6]);
+            bad_obj = bad_obj || x[7] != 0.0;
+        }
+        if (bad_obj) { ptb_scene_destroy(s); set_error("tri_obj out of range"); return PTB_ERR_ARG; }
+    } else {
+        for (size_t i = 0; i < (size_t)n * 9; ++i) scale = std::max(scale, fabs(desc->verts[i]));
+        for (size_t i = 0; i < (size_t)n * 3; ++i)
+            for (int k = 0; k < 3; ++k) { blo[k] = std::min(blo[k], desc->verts[3 * i + k]); bhi[k] = std::max(bhi[k], desc->verts[3 * i + k]); }
+    }
+    pt_.mark("upload + extent (wait)");
+    for (int i = 0; i < 3; ++i) scale = std::max(scale, fabs(desc->eye[i]));
+    s->dt_scale = (float)(32.0 * 5.9604644775390625e-08 * scale);
+    for (int k = 0; k < 3; ++k) { d.bb_lo[k] = (float)blo[k]; d.bb_inv[k] = (float)(256.0 / std::max(bhi[k] - blo[k], 1e-30)); }
+
+    if (dev_records) {
+        TriRec *d_tri = nullptr; float4 *d_sn = nullptr;
+        if (scene_malloc((void **)&d_tri, sizeof(TriRec) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(d_tri);
+        if (scene_malloc((void **)&d_sn, sizeof(float4) * (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(d_sn);
+        k_make_records<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, d.normals64, d.tri_obj, n, scale, d_tri, d_sn);
+        ++g_launches;
+        d.tri = d_tri; d.tri_sn = d_sn; d.tri_id = nullptr;
+    } else {
+        tri.resize(n); sn.resize(n); ids.resize(n);
+        for (int i = 0; i < n; ++i) {
+            if (desc->tri_obj[i] < 0 || desc->tri_obj[i] > no) { delete s; set_error("tri_obj[%d] out of range", i); return PTB_ERR_ARG; }
+            tri[i] = make_trirec(desc->verts + 9 * (size_t)i, desc->tri_obj[i], scale);
+            tri[i].q3.w = bits_f(i);                     // reference index travels with the record (LBVH leaf order)
+            const double *nn = desc->normals + 3 * (size_t)i;
+            sn[i] = make_float4((float)nn[0], (float)nn[1], (float)nn[2], bits_f(desc->tri_obj[i]));
+            ids[i] = i;
+        }
+    }
+    pt_.mark("records");
     std::vector<PlaneRec> planes; int n_occ = 0;
     if (accel == PTB_ACCEL_BRUTE) build_plane_groups(desc, tri, planes, n_occ);
 
@@ -591,7 +606,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         ptb_scene_destroy(s);
         return rc;
     }
-    pt_.mark("obj_first + small uploads");
+    pt_.mark("small uploads");
     d.n_tri = n; d.n_tri_obj = desc->n_tri_obj; d.n_obj = no; d.n_light_tri = desc->n_light_tri;
     d.accel = accel;
     for (int i = 0; i < 3; ++i) { d.eye[i] = desc->eye[i]; d.light_color[i] = desc->light_color[i]; }
