@@ -250,7 +250,7 @@ static void build_plane_groups(const ptb_scene_desc *desc, const std::vector<Tri
 // for a wall.  n_objs = number of object ids among the n triangles.
 static size_t lbvh_arena_bytes(int n, int n_objs) {      // upper bound of what build_lbvh carves (sum of its temporaries)
     const size_t nn = (size_t)n, tiles = (nn + PS_TILE - 1) / PS_TILE;
-    return nn * (2 * sizeof(Aabb) + sizeof(float4) + sizeof(int2) + 4 * 9 + 8) + 4 * 256 * tiles + (size_t)n_objs * 52 + 64 * 256;
+    return nn * (2 * sizeof(Aabb) + sizeof(float4) + sizeof(int2) + 4 * 9 + 8 + 1) + 4 * 256 * tiles + (size_t)n_objs * 52 + 64 * 256;
 }
 
 static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
@@ -263,6 +263,7 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
     int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
     unsigned *ghist = nullptr, *flags = nullptr, *totals = nullptr, *d_n = nullptr; BvhNode *nodes = nullptr; TriRec *tri_sorted = nullptr;
     unsigned *obj_box = nullptr, *morton_orig = nullptr; unsigned long long *key64 = nullptr; float *obj_lo = nullptr, *obj_inv = nullptr; int *rank = nullptr;
+    unsigned char *node_pid = nullptr;
     // temporaries are carved out of ONE arena owned by the caller (both trees of a scene share it): twenty-odd cudaMalloc /
     // cudaFree pairs per tree cost ten times the 1.6 ms the build kernels take (cudaFree synchronises the device)
     struct Want { void **p; size_t bytes; bool keep; };
@@ -278,6 +279,7 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
         {(void **)&obj_box, 24 * (size_t)n_objs, false}, {(void **)&morton_orig, 4 * (size_t)n, false},
         {(void **)&key64, 8 * (size_t)n, false}, {(void **)&obj_lo, 12 * (size_t)n_objs, false},
         {(void **)&obj_inv, 12 * (size_t)n_objs, false}, {(void **)&rank, 4 * (size_t)n_objs, false},
+        {(void **)&node_pid, (size_t)n, false},
         {(void **)&nodes, sizeof(BvhNode) * (size_t)n, true}, {(void **)&tri_sorted, sizeof(TriRec) * (size_t)n, true}};
     size_t at = 0;
     for (const Want &w : wants) {
@@ -355,8 +357,8 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
         ++g_launches;
         cudaMemsetAsync(flags, 0, 4 * (size_t)n, st);
         k_karras<<<g, 256, 0, st>>>(key64, n, child, parent_inner, parent_leaf);
-        k_refit<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, parent_inner, parent_leaf, node_box, node_minref, flags);
-        k_pack<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, node_box, node_minref, s->pad, nodes);
+        k_refit<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, parent_inner, parent_leaf, node_box, node_minref, flags, d.tri_pid, node_pid);
+        k_pack<<<g, 256, 0, st>>>(n, vals[1], tri_box, child, node_box, node_minref, s->pad, nodes, d.tri_pid, node_pid);
         k_gather_tris<<<g, 256, 0, st>>>(n, vals[1], src_tri, tri_sorted);
         g_launches += 4;
     }
@@ -381,22 +383,22 @@ extern "C" int ptb_version(void) { return 100; }
 // ---- replicated hierarchies (ptb_bvh_export / ptb_bvh_import): one device buffer = header + six sections
 struct BvhBlobHeader {
     unsigned magic, version;
-    int n_tri, n_tri_obj, has_occ;
+    int n_tri, n_tri_obj, has_occ, has_pid;
     float pad;
-    unsigned long long off[6];      // nodes, tri, ids, nodes_occ, tri_occ, ids_occ (bytes from the start of the buffer)
+    unsigned long long off[7];      // nodes, tri, ids, nodes_occ, tri_occ, ids_occ, plane ids (bytes from the start of the buffer)
     unsigned long long total;
 };
-static const unsigned BVH_BLOB_MAGIC = 0x56425450u /* "PTBV" */, BVH_BLOB_VERSION = 1u;
-static BvhBlobHeader bvh_blob_layout(int n_tri, int n_tri_obj, bool has_occ, float pad) {
+static const unsigned BVH_BLOB_MAGIC = 0x56425450u /* "PTBV" */, BVH_BLOB_VERSION = 2u;
+static BvhBlobHeader bvh_blob_layout(int n_tri, int n_tri_obj, bool has_occ, bool has_pid, float pad) {
     BvhBlobHeader h;
     memset(&h, 0, sizeof(h));
     h.magic = BVH_BLOB_MAGIC; h.version = BVH_BLOB_VERSION;
-    h.n_tri = n_tri; h.n_tri_obj = n_tri_obj; h.has_occ = has_occ ? 1 : 0; h.pad = pad;
+    h.n_tri = n_tri; h.n_tri_obj = n_tri_obj; h.has_occ = has_occ ? 1 : 0; h.has_pid = has_pid ? 1 : 0; h.pad = pad;
     const size_t no = has_occ ? (size_t)n_tri_obj : 0;
-    const size_t bytes[6] = {sizeof(BvhNode) * (size_t)n_tri, sizeof(TriRec) * (size_t)n_tri, 4 * (size_t)n_tri,
-                             sizeof(BvhNode) * no, sizeof(TriRec) * no, 4 * no};
+    const size_t bytes[7] = {sizeof(BvhNode) * (size_t)n_tri, sizeof(TriRec) * (size_t)n_tri, 4 * (size_t)n_tri,
+                             sizeof(BvhNode) * no, sizeof(TriRec) * no, 4 * no, has_pid ? (size_t)n_tri : 0};
     size_t at = 256;
-    for (int i = 0; i < 6; ++i) { h.off[i] = at; at += (bytes[i] + 255) & ~(size_t)255; }
+    for (int i = 0; i < 7; ++i) { h.off[i] = at; at += (bytes[i] + 255) & ~(size_t)255; }
     h.total = at;
     return h;
 }
@@ -577,6 +579,26 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         k_make_records<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, d.normals64, d.tri_obj, n, scale, d_tri, d_sn);
         ++g_launches;
         d.tri = d_tri; d.tri_sn = d_sn; d.tri_id = nullptr;
+        // supporting-plane ids (ptb_bvh_build.cuh): a received hierarchy brings its own numbering (ptb_bvh_import)
+        if (!d_blob && getenv("PTB_NO_PLANE_CULL") == nullptr) {
+            unsigned char *d_pid = nullptr; unsigned long long *d_table = nullptr;
+            if (scene_malloc((void **)&d_pid, (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+            s->allocs.push_back(d_pid);
+            if (scene_malloc((void **)&d_table, 8 * (PTB_PLANE_IDS + 2), st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+            cudaMemsetAsync(d_table, 0, 8 * (PTB_PLANE_IDS + 2), st);
+            // normals within q_n and offsets within q_d: q_n * diameter and q_d stay 4 x below sqrt(1e-5) * 1e-5 = 3.2e-8
+            double diam = 0.0;
+            for (int k = 0; k < 3; ++k) diam = std::max(diam, bhi[k] - blo[k]);
+            const double q_n = std::min(2e-10, 8e-9 / (2.0 * std::max(diam, 1e-30))), q_d = 8e-9;
+            k_plane_ids<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, n, q_n, q_d, d_table, d_pid);
+            ++g_launches;
+            unsigned long long overflow = 0;
+            cudaMemcpyAsync(&overflow, d_table + PTB_PLANE_IDS + 1, 8, cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaStreamSynchronize(st);
+            cudaFreeAsync(d_table, st);
+            if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("plane ids: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
+            d.tri_pid = overflow ? nullptr : d_pid;      // more planes than ids (a soup): no plane culling for this scene
+        }
     } else {
         tri.resize(n); sn.resize(n); ids.resize(n);
         for (int i = 0; i < n; ++i) {
@@ -631,17 +653,18 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
                 ptb_scene_destroy(s); set_error("ptb_bvh_import: cannot read the buffer header"); return PTB_ERR_CUDA;
             }
             const bool want_occ = d.n_tri_obj >= 2;
-            const BvhBlobHeader w = bvh_blob_layout(n, d.n_tri_obj, want_occ, s->pad);
+            const BvhBlobHeader w = bvh_blob_layout(n, d.n_tri_obj, want_occ, h.has_pid == 1, s->pad);
             if (h.magic != BVH_BLOB_MAGIC || h.version != BVH_BLOB_VERSION || h.n_tri != n || h.n_tri_obj != d.n_tri_obj ||
-                h.has_occ != w.has_occ || h.pad != s->pad || h.total != w.total || blob_bytes < w.total) {
+                h.has_occ != w.has_occ || (h.has_pid != 0 && h.has_pid != 1) || h.pad != s->pad || h.total != w.total || blob_bytes < w.total) {
                 ptb_scene_destroy(s);
                 set_error("ptb_bvh_import: buffer does not belong to this scene (magic %08x version %u, %d/%d triangles, %llu bytes; expected %d/%d, %llu)",
                           h.magic, h.version, h.n_tri, h.n_tri_obj, (unsigned long long)h.total, n, d.n_tri_obj, (unsigned long long)w.total);
                 return PTB_ERR_ARG;
             }
-            void *sec[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-            for (int i = 0; i < (want_occ ? 6 : 3); ++i) {
-                const size_t bytes = (size_t)((i + 1 < 6 ? w.off[i + 1] : w.total) - w.off[i]);
+            void *sec[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+            for (int i = 0; i < 7; ++i) {
+                const size_t bytes = (size_t)((i + 1 < 7 ? w.off[i + 1] : w.total) - w.off[i]);
+                if (bytes == 0) continue;          // no occlusion tree / no plane ids
                 if (scene_malloc(&sec[i], bytes, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
                 s->allocs.push_back(sec[i]);
                 if (cudaMemcpyAsync(sec[i], (const char *)d_blob + w.off[i], bytes, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
@@ -650,6 +673,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             }
             d.nodes = (const BvhNode *)sec[0]; d.tri = (const TriRec *)sec[1]; d.tri_id = (const int *)sec[2];
             d.nodes_occ = (const BvhNode *)sec[3]; d.tri_occ = (const TriRec *)sec[4]; d.tri_id_occ = (const int *)sec[5];
+            d.tri_pid = (const unsigned char *)sec[6];
             s->build_ms = 0.0;
             s->n_nodes = n - 1;
         } else {
@@ -697,26 +721,26 @@ extern "C" int ptb_scene_info(const ptb_scene *s, int32_t *accel, int32_t *n_nod
 
 extern "C" size_t ptb_bvh_export_bytes(const ptb_scene *s) {
     if (!s || s->d.accel != PTB_ACCEL_LBVH || !s->d.nodes) return 0;
-    return (size_t)bvh_blob_layout(s->d.n_tri, s->d.n_tri_obj, s->d.nodes_occ != nullptr, s->pad).total;
+    return (size_t)bvh_blob_layout(s->d.n_tri, s->d.n_tri_obj, s->d.nodes_occ != nullptr, s->d.tri_pid != nullptr, s->pad).total;
 }
 
 extern "C" int ptb_bvh_export(const ptb_scene *s, void *d_blob, size_t blob_bytes, void *stream) {
     if (!s || !d_blob) { set_error("ptb_bvh_export: null argument"); return PTB_ERR_ARG; }
     if (s->d.accel != PTB_ACCEL_LBVH || !s->d.nodes) { set_error("ptb_bvh_export: the scene has no LBVH (shared-memory plane list)"); return PTB_ERR_UNSUPPORTED; }
     const DScene &d = s->d;
-    const BvhBlobHeader h = bvh_blob_layout(d.n_tri, d.n_tri_obj, d.nodes_occ != nullptr, s->pad);
+    const BvhBlobHeader h = bvh_blob_layout(d.n_tri, d.n_tri_obj, d.nodes_occ != nullptr, d.tri_pid != nullptr, s->pad);
     if (blob_bytes < h.total) { set_error("ptb_bvh_export: buffer of %zu bytes, %llu needed", blob_bytes, (unsigned long long)h.total); return PTB_ERR_NOMEM; }
     cudaStream_t st = (cudaStream_t)stream;
     // zero the header block and the alignment gaps so equal scenes export equal buffers
     PTB_CUDA(cudaMemsetAsync(d_blob, 0, 256, st));
     PTB_CUDA(cudaMemcpyAsync(d_blob, &h, sizeof(h), cudaMemcpyHostToDevice, st));
-    const void *src[6] = {d.nodes, d.tri, d.tri_id, d.nodes_occ, d.tri_occ, d.tri_id_occ};
+    const void *src[7] = {d.nodes, d.tri, d.tri_id, d.nodes_occ, d.tri_occ, d.tri_id_occ, d.tri_pid};
     const size_t no = h.has_occ ? (size_t)d.n_tri_obj : 0;
     // a tree over n leaves has n - 1 nodes; the n-th slot of the node array is never written by the build
-    const size_t used[6] = {sizeof(BvhNode) * (size_t)(d.n_tri - 1), sizeof(TriRec) * (size_t)d.n_tri, 4 * (size_t)d.n_tri,
-                            no ? sizeof(BvhNode) * (no - 1) : 0, sizeof(TriRec) * no, 4 * no};
-    for (int i = 0; i < 6; ++i) {
-        const size_t span = (size_t)((i + 1 < 6 ? h.off[i + 1] : h.total) - h.off[i]);
+    const size_t used[7] = {sizeof(BvhNode) * (size_t)(d.n_tri - 1), sizeof(TriRec) * (size_t)d.n_tri, 4 * (size_t)d.n_tri,
+                            no ? sizeof(BvhNode) * (no - 1) : 0, sizeof(TriRec) * no, 4 * no, d.tri_pid ? (size_t)d.n_tri : 0};
+    for (int i = 0; i < 7; ++i) {
+        const size_t span = (size_t)((i + 1 < 7 ? h.off[i + 1] : h.total) - h.off[i]);
         if (used[i]) PTB_CUDA(cudaMemcpyAsync((char *)d_blob + h.off[i], src[i], used[i], cudaMemcpyDeviceToDevice, st));
         if (span > used[i]) PTB_CUDA(cudaMemsetAsync((char *)d_blob + h.off[i] + used[i], 0, span - used[i], st));
     }

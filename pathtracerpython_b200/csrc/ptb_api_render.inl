@@ -84,7 +84,8 @@ static bool g_count_nodes = false;   // instrumented (untimed) run: count nodes 
 
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
-                            bool track, float *hit_t, int *hit_tri, cudaStream_t st, const unsigned *order = nullptr) {
+                            bool track, float *hit_t, int *hit_tri, cudaStream_t st, const unsigned *order = nullptr,
+                            const int *origin_pid = nullptr) {
     ProfScope ps_(PK_CLOSEST, st);
     if (s->d.accel == PTB_ACCEL_LBVH) {
         const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
@@ -93,6 +94,10 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (track)
                 k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
+            else if (origin_pid && g_count_nodes)
+                k_closest_bvh32_dyn<false, true, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
+            else if (origin_pid)
+                k_closest_bvh32_dyn<false, false, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
             else if (g_count_nodes)
                 k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else
@@ -275,11 +280,16 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
     }
     const bool sorting = d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic && s->sort_rays && q.sort.keys[0];
     const unsigned *order = nullptr;       // visiting order of the live slots of queue `in` (null: slot order)
+    // plane id of the triangle every live path stands on, per output slot of the shade kernel (the second hit-record set
+    // belongs to the fused small-scene pipeline and is free here): read by the shadow rays of this bounce and by the
+    // closest-hit rays of the next one (ptb_bvh_dyn.cuh, PID)
+    int *origin_pid = (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic && d.tri_pid) ? q.hit_tri2 : nullptr;
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
         const bool track = (b == 0) && !(p->flags & PTB_FLAG_NO_FP64_RETRACE);
-        if ((rc = launch_closest32(s, q, in, q.count + b, b == 0 ? n_primary : N, track, q.hit_t, q.hit_tri, st, order))) return rc;
+        if ((rc = launch_closest32(s, q, in, q.count + b, b == 0 ? n_primary : N, track, q.hit_t, q.hit_tri, st, order,
+                                   b == 0 ? nullptr : origin_pid))) return rc;
         if (track) {
             { ProfScope ps_(PK_RETRACE, st);
             k_retrace64<<<grid_for(n_primary / 8 + 1, 128, 4), 128, 0, st>>>(d, bi.pm, bi.npix, q.unc_count, q.unc_list, q.hit_t, q.hit_tri);
@@ -289,7 +299,7 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         { ProfScope ps_(PK_SHADE, st);
         k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
-            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr, (share && b == 0) ? 1 : 0);
+            q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr, (share && b == 0) ? 1 : 0, origin_pid);
         }
         PTB_LAUNCHED();
         if (sorting) {      // order the survivors by the Morton key of their new origin (ptb_sort.cuh)
@@ -309,7 +319,11 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         if (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic) {
             unsigned *work = q.work + (g_work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
-            if (g_count_nodes)
+            if (origin_pid && g_count_nodes)
+                k_shadow_bvh32_dyn<true, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
+            else if (origin_pid)
+                k_shadow_bvh32_dyn<false, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
+            else if (g_count_nodes)
                 k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             else
                 k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);

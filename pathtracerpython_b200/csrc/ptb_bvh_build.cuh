@@ -191,7 +191,8 @@ __device__ __forceinline__ Aabb ld_box_cg(const Aabb *p) {
 __global__ void __launch_bounds__(256)
 k_refit(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_box, const int2 *__restrict__ child,
         const int *__restrict__ parent_inner, const int *__restrict__ parent_leaf, Aabb *__restrict__ node_box,
-        int *__restrict__ node_minref, unsigned *__restrict__ flags) {
+        int *__restrict__ node_minref, unsigned *__restrict__ flags, const unsigned char *__restrict__ tri_pid,
+        unsigned char *__restrict__ node_pid) {
     for (int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < n; leaf += gridDim.x * blockDim.x) {
         int node = parent_leaf[leaf];
         while (node >= 0) {
@@ -199,11 +200,13 @@ k_refit(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_
             __threadfence();
             const int2 c = child[node];
             Aabb a, b; int ra, rb;
+            unsigned pa = 0, pb = 0;
             // children written by other threads: read through L2 (L1 may hold a stale neighbouring line)
-            if (c.x < 0) { a = tri_box[sorted_tri[~c.x]]; ra = sorted_tri[~c.x]; }
-            else { a = ld_box_cg(node_box + c.x); ra = __ldcg(node_minref + c.x); }
-            if (c.y < 0) { b = tri_box[sorted_tri[~c.y]]; rb = sorted_tri[~c.y]; }
-            else { b = ld_box_cg(node_box + c.y); rb = __ldcg(node_minref + c.y); }
+            if (c.x < 0) { a = tri_box[sorted_tri[~c.x]]; ra = sorted_tri[~c.x]; if (tri_pid) pa = tri_pid[ra]; }
+            else { a = ld_box_cg(node_box + c.x); ra = __ldcg(node_minref + c.x); if (tri_pid) pa = __ldcg(node_pid + c.x); }
+            if (c.y < 0) { b = tri_box[sorted_tri[~c.y]]; rb = sorted_tri[~c.y]; if (tri_pid) pb = tri_pid[rb]; }
+            else { b = ld_box_cg(node_box + c.y); rb = __ldcg(node_minref + c.y); if (tri_pid) pb = __ldcg(node_pid + c.y); }
+            if (tri_pid) node_pid[node] = (unsigned char)(pa == pb ? pa : 0u);     // one plane below the node, or mixed
             Aabb r;
 #pragma unroll
             for (int k = 0; k < 3; ++k) { r.lo[k] = fminf(a.lo[k], b.lo[k]); r.hi[k] = fmaxf(a.hi[k], b.hi[k]); }
@@ -218,7 +221,8 @@ k_refit(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_
 // final 64 B nodes; boxes inflated by `pad`
 __global__ void __launch_bounds__(256)
 k_pack(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_box, const int2 *__restrict__ child,
-       const Aabb *__restrict__ node_box, const int *__restrict__ node_minref, float pad, BvhNode *__restrict__ nodes) {
+       const Aabb *__restrict__ node_box, const int *__restrict__ node_minref, float pad, BvhNode *__restrict__ nodes,
+       const unsigned char *__restrict__ tri_pid, const unsigned char *__restrict__ node_pid) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
         const int2 c = child[i];
         const Aabb a = c.x < 0 ? tri_box[sorted_tri[~c.x]] : node_box[c.x];
@@ -228,9 +232,12 @@ k_pack(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_b
         nd.hi0x = a.hi[0] + pad; nd.hi0y = a.hi[1] + pad; nd.hi0z = a.hi[2] + pad;
         nd.lo1x = b.lo[0] - pad; nd.lo1y = b.lo[1] - pad; nd.lo1z = b.lo[2] - pad;
         nd.hi1x = b.hi[0] + pad; nd.hi1y = b.hi[1] + pad; nd.hi1z = b.hi[2] + pad;
-        nd.c0 = c.x; nd.c1 = c.y;
         nd.n0 = c.x < 0 ? sorted_tri[~c.x] : node_minref[c.x];     // lowest reference index below child 0 / 1
         nd.n1 = c.y < 0 ? sorted_tri[~c.y] : node_minref[c.y];
+        unsigned p0 = 0, p1 = 0;
+        if (tri_pid) { p0 = c.x < 0 ? tri_pid[nd.n0] : node_pid[c.x]; p1 = c.y < 0 ? tri_pid[nd.n1] : node_pid[c.y]; }
+        nd.c0 = c.x;                                               // child 1 is position(child 0) + 1 (k_karras)
+        nd.meta = (int)((c.y < 0 ? 0x80000000u : 0u) | (p1 << 8) | p0);
         nodes[i] = nd;
     }
 }
@@ -303,6 +310,50 @@ k_make_records(const double *__restrict__ verts, const double *__restrict__ norm
         tri[i] = r;
         const double *sn = normals + 3 * (size_t)i;
         tri_sn[i] = make_float4((float)sn[0], (float)sn[1], (float)sn[2], __int_as_float(obj));
+    }
+}
+
+// Supporting-plane ids.  Two triangles get the same id when their unit normals (sign-normalised) agree to q_n per
+// component and their plane offsets to q_d: with q_n * (scene diameter) and q_d far below sqrt(1e-5) * 1e-5 = 3.2e-8 a
+// line that starts on one of them cannot meet the other one outside the reference's self-hit guard (it would need
+// |t| > sqrt(1e-5) with |n.d| > 1e-5, main.py:47-48, 100, utils.py:117), so skipping it is exact, not a heuristic.
+// table: PTB_PLANE_IDS + 1 keys (0 = empty) filled with atomicCAS; table[PTB_PLANE_IDS + 1] counts overflows - more
+// planes than ids - and then the scene goes without (the caller checks): which planes got an id would depend on the
+// race.  The NUMBERING depends on it too, but only equality of ids is ever used.
+__device__ __forceinline__ unsigned long long pid_mix(unsigned long long h, long long v) {
+    h ^= (unsigned long long)v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+    h ^= h >> 30; h *= 0xbf58476d1ce4e5b9ull; h ^= h >> 27; h *= 0x94d049bb133111ebull; h ^= h >> 31;
+    return h;
+}
+__global__ void __launch_bounds__(256)
+k_plane_ids(const double *__restrict__ verts, int n, double q_n, double q_d, unsigned long long *table, unsigned char *__restrict__ tri_pid) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double *A = verts + 9 * (size_t)i, *B = A + 3, *C = A + 6;
+        double e1[3], e2[3], nn[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { e1[k] = xsub(B[k], A[k]); e2[k] = xsub(C[k], A[k]); }
+        hcross(e1, e2, nn);
+        const double nl = xsqrt(hdot(nn, nn));
+        unsigned id = 0;
+        if (nl > 0.0 && nl == nl) {
+            int big = 0;
+            if (fabs(nn[1]) > fabs(nn[big])) big = 1;
+            if (fabs(nn[2]) > fabs(nn[big])) big = 2;
+            const double sg = (nn[big] < 0.0 ? -1.0 : 1.0) / nl;
+            const double d0 = hdot(nn, A) * sg;
+            unsigned long long key = pid_mix(pid_mix(pid_mix(pid_mix(0x1234567ull, llrint(nn[0] * sg / q_n)), llrint(nn[1] * sg / q_n)),
+                                                     llrint(nn[2] * sg / q_n)), llrint(d0 / q_d));
+            if (key == 0ull) key = 1ull;
+            unsigned slot = (unsigned)(key % PTB_PLANE_IDS);
+            for (int probe = 0; probe < PTB_PLANE_IDS; ++probe) {
+                unsigned long long cur = __ldcg(table + slot);
+                if (cur == 0ull) cur = atomicCAS(table + slot, 0ull, key);
+                if (cur == 0ull || cur == key) { id = slot + 1u; break; }
+                slot = slot + 1u == PTB_PLANE_IDS ? 0u : slot + 1u;
+            }
+            if (id == 0u) atomicAdd(table + PTB_PLANE_IDS + 1, 1ull);
+        }
+        tri_pid[i] = (unsigned char)id;
     }
 }
 

@@ -59,15 +59,18 @@ __device__ __forceinline__ unsigned claim_work(bool want, unsigned *work, unsign
 
 // ---------------------------------------------------------------- closest hit
 // PHYS (physical mode): ray semantics, only t > tmin counts; boxes behind the origin are skipped.
-template <bool TRACK, bool COUNT, bool PHYS = false>
+// PID: origin_pid[ray] = supporting-plane id of the triangle the ray starts on (0: none).  Children whose triangles all
+// lie in that plane are skipped without a box test: the line meets them at t = 0, inside the self-hit guard
+// (ptb_scene.cuh, k_plane_ids).  For rays leaving a wall this removes the walk down to the origin's own leaf.
+template <bool TRACK, bool COUNT, bool PHYS = false, bool PID = false>
 __global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
 k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__restrict__ qd, const unsigned *__restrict__ d_count,
                     float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
-                    unsigned *work, const unsigned *__restrict__ order) {
+                    unsigned *work, const unsigned *__restrict__ order, const int *__restrict__ origin_pid = nullptr) {
     const unsigned count = *d_count;
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
-    int sp = 0, node = 0, best_ref = 0x7fffffff;
+    int sp = 0, node = 0, best_ref = 0x7fffffff, opid = -1;
     unsigned ray = 0xffffffffu;
     bool exhausted = false;                 // warp-uniform: the pool ran dry
     Hit32 h; h.t = 0.f; h.abs_t = 0.f; h.slot = -1;
@@ -86,6 +89,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 h.t = 0.f; h.abs_t = 3.0e38f; h.slot = -1; best_ref = 0x7fffffff;
                 uc.init();
                 sp = 0; node = 0;
+                if (PID) { const int pr = origin_pid[ray]; opid = pr ? pr : -1; }
             }
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
         }
@@ -105,6 +109,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 go0 = go0 && (far_abs(tn0, tf0) >= PTB_TMIN_SAFE);
                 go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             }
+            if (PID) { go0 = go0 && (n.pid0 != opid); go1 = go1 && (n.pid1 != opid); }
             // leaf children: one shared test block walked up to twice, so lanes with a single leaf child (either side)
             // run it together instead of the warp stepping through a copy per side
             const bool leaf0 = go0 && c0 < 0, leaf1 = go1 && c1 < 0;
@@ -180,10 +185,11 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
 // sh_res[s * cap + j] = occluding object index (lowest one for s == 2), or -1
 // PHYS: plain any-hit ray query for every light sample (t in (tmin, distance)); the outcome array holds the
 // sample's FLOAT weight written by the shade kernel and an occluded sample is zeroed (ptb_phys.cuh).
-template <bool COUNT, bool PHYS = false>
+template <bool COUNT, bool PHYS = false, bool PID = false>
 __global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
 k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restrict__ sh_d, const unsigned *__restrict__ d_count,
-                   int *__restrict__ sh_res, int cap, unsigned *work, const unsigned *__restrict__ order) {
+                   int *__restrict__ sh_res, int cap, unsigned *work, const unsigned *__restrict__ order,
+                   const int *__restrict__ origin_pid = nullptr) {
     // occlusion tree: object triangles only (main.py:42); the full tree + min-ref pruning when it does not exist
     const BvhNode *__restrict__ nodes = sc.nodes_occ ? sc.nodes_occ : sc.nodes;
     const TriRec *__restrict__ tris = sc.nodes_occ ? sc.tri_occ : sc.tri;
@@ -197,7 +203,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
 #endif
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
-    int sp = 0, node = 0, found = 0x7fffffff, found_obj = -1;
+    int sp = 0, node = 0, found = 0x7fffffff, found_obj = -1, opid = -1;
     unsigned item = 0xffffffffu, out_slot = 0;
     bool exhausted = false, want_min = false;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(1.f, 0.f, 0.f);
@@ -226,6 +232,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                 want_min = !PHYS && s == 2u;
                 found = 0x7fffffff; found_obj = -1;
                 sp = 0; node = 0;
+                if (PID) { const int pr = origin_pid[j]; opid = pr ? pr : -1; }
             }
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
         }
@@ -249,6 +256,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                     go0 = go0 && (tf0 >= -lim) && (fmaxf(-tn0, tf0) >= PTB_TMIN_SAFE);
                     go1 = go1 && (tf1 >= -lim) && (fmaxf(-tn1, tf1) >= PTB_TMIN_SAFE);
                 }
+                if (PID) { go0 = go0 && (n.pid0 != opid); go1 = go1 && (n.pid1 != opid); }
 #if PTB_FLAT_STEP_SHADOW
                 {
                     const bool both = go0 && go1, any = go0 || go1;

@@ -63,16 +63,21 @@ __device__ __forceinline__ void ld256(const void *p, float4 &lo, float4 &hi) {
 #endif
 }
 
-struct NodeBoxes { float4 a, b, c; int4 d; };
+struct NodeBoxes { float4 a, b, c; int4 d; int pid0, pid1; };
 __device__ __forceinline__ NodeBoxes ld_node(const BvhNode *nodes, int i) {
     const float4 *p = reinterpret_cast<const float4 *>(nodes + i);
     NodeBoxes n;
     float4 w;
     ld256(p, n.a, n.b); ld256(p + 2, n.c, w);
-    n.d = make_int4(__float_as_int(w.x), __float_as_int(w.y), __float_as_int(w.z), __float_as_int(w.w));
+    // child 1 = position of child 0 plus one, leaf flag in meta's sign (ptb_scene.cuh)
+    const int c0 = __float_as_int(w.x), meta = __float_as_int(w.y);
+    const int i1 = (c0 ^ (c0 >> 31)) + 1;
+    n.d = make_int4(c0, i1 ^ (meta >> 31), __float_as_int(w.z), __float_as_int(w.w));
+    n.pid0 = meta & 0xff; n.pid1 = (meta >> 8) & 0xff;      // dead code in the kernels that do not use them
     return n;
 }
-// BvhNode layout as float4s: a = lo0.xyz hi0.x ; b = hi0.yz lo1.xy ; c = lo1.z hi1.xyz ; d = c0 c1 minref0 minref1
+// BvhNode layout as float4s: a = lo0.xyz hi0.x ; b = hi0.yz lo1.xy ; c = lo1.z hi1.xyz ; d = c0 meta minref0 minref1
+// (NodeBoxes.d is c0 c1 minref0 minref1)
 
 // ---------------------------------------------------------------- FP32 closest hit
 // TRACK: prune with best |t| + its error bound and collect uncertainty (ptb_isect.cuh) so uncertain

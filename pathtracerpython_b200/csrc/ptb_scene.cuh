@@ -14,12 +14,19 @@ struct TriRec { float4 q0, q1, q2, q3; };
 
 // BVH2 node, 64 B: both children's boxes inline so one fetch decides both descents.
 //   lo0.xyz hi0.xyz = child 0 box, lo1.xyz hi1.xyz = child 1 box,
-//   c0 / c1 = child index (>= 0 inner node, < 0 : leaf, triangle slot = ~c)
+//   c0 = child 0 (>= 0 inner node, < 0 : leaf, triangle slot = ~c).  In a Karras tree the children of a node are the
+//   positions gamma and gamma + 1 (ptb_bvh_build.cuh), so child 1 is "index of child 0, plus one" and only its
+//   leaf / inner flag needs storing: meta bit 31 = child 1 is a leaf.  The room that frees holds the PLANE ID of either
+//   child, meta bits 0..7 / 8..15: k > 0 when every triangle below the child lies in supporting plane k, else 0.
+//   A line that starts on a triangle of plane k meets every other triangle of that plane at t = 0, inside the
+//   self-hit guard (main.py:47-48, 100: d^2 > 1e-5), so such subtrees are skipped without a box test (ptb_bvh_dyn.cuh).
+//   n0 / n1 = lowest reference index below the child.
 struct BvhNode {
     float lo0x, lo0y, lo0z, hi0x, hi0y, hi0z;
     float lo1x, lo1y, lo1z, hi1x, hi1y, hi1z;
-    int c0, c1, n0, n1;   // n0/n1: triangle count under the child (leaf: 1)
+    int c0, meta, n0, n1;
 };
+#define PTB_PLANE_IDS 255        // plane ids 1..255; 0 = none / mixed
 
 struct DScene {
     // --- FP32 product path
@@ -45,6 +52,7 @@ struct DScene {
     const BvhNode *nodes_occ; // BVH over the occlusion set (object triangles only)
     const TriRec *tri_occ;    // leaf-ordered records of the occlusion set
     const int *tri_id_occ;
+    const unsigned char *tri_pid; // [n_tri] by reference index: supporting-plane id of the triangle (0: none); null when unused
     int n_tri, n_tri_obj, n_obj, n_light_tri;
     int accel;
     double eye[3], ortho[4], ambient, light_color[3];

@@ -159,7 +159,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
           const float *__restrict__ hit_t, const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in,
           unsigned *d_count_out, float4 *__restrict__ qo_out, float4 *__restrict__ qd_out,
           float4 *__restrict__ sh_p, float4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, float4 *__restrict__ L,
-          int cap, RecPtrs rec, unsigned *__restrict__ sort_keys, int share_primary) {
+          int cap, RecPtrs rec, unsigned *__restrict__ sort_keys, int share_primary, int *__restrict__ origin_pid = nullptr) {
     // share_primary (bounce 0 only): every sample of a pixel starts with the same primary ray (main.py:191,
     // A-Q14), so the ray and its closest hit are stored once per pixel slot and read by all S samples
     const unsigned count = share_primary ? (unsigned)bi.npix * (unsigned)bi.S : *d_count_in;
@@ -210,6 +210,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         for (int s = 0; s < 3; ++s) sh_d[(size_t)s * cap + j] = ld[s];
         sh_p[j] = make_float4(P.x, P.y, P.z, k);
         sh_aux[j] = make_int2(id, tri);
+        if (origin_pid) origin_pid[j] = (int)__ldg(sc.tri_pid + tri);     // plane the new rays start on (ptb_bvh_dyn.cuh)
         if (sort_keys) sort_keys[j] = ps_key(P.x, P.y, P.z, sc.bb_lo, sc.bb_inv);
 
         // ---- bounce (main.py:240-264)
