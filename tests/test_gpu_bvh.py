@@ -286,3 +286,52 @@ def test_bvh_export_import_is_bitwise_identical(cornell, tess8):
     with pytest.raises(ptb.PtbError, match="no LBVH"):
         small.export_bvh()
     small.close(); built.close(); imp.close()
+
+
+def _has_plane_ids(r):
+    import struct
+    return struct.unpack("<i", r.export_bvh()[20:24].cpu().numpy().tobytes())[0]
+
+
+def test_plane_culling_changes_no_outcome(cornell, tess8, monkeypatch):
+    """Supporting-plane ids (k_plane_ids): subtrees lying in the plane a ray starts on are skipped.  Under the
+    reference's self-hit guard (d^2 > 1e-5, main.py:47-48, 100) those triangles are never hits, so every record must be
+    what the walk without the rule produces - up to the few FP32 grazing rays whose own plane the unculled walk
+    'hits' at |t| > sqrt(1e-5) through rounding of the origin (the reference, in FP64, never does)."""
+    on = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
+    monkeypatch.setenv("PTB_NO_PLANE_CULL", "1")
+    off = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
+    monkeypatch.delenv("PTB_NO_PLANE_CULL")
+    assert _has_plane_ids(on) == 1 and _has_plane_ids(off) == 0
+    a1, r1 = on.trace_paths(3, 4, seed=17, width=96, height=96, records=True)
+    a0, r0 = off.trace_paths(3, 4, seed=17, width=96, height=96, records=True)
+    r1, r0 = _np(r1), _np(r0)
+    same = _sig(r1, r0)
+    assert (~same).mean() < 2e-4, (~same).mean()
+    assert np.array_equal(r1["contrib"][same], r0["contrib"][same])            # identical arithmetic where histories agree
+    # the culled walk is the one that agrees with the FP64 oracle where the two differ
+    ref = oracle.Oracle(tess8.flatten(), 96, 96).trace(3, 4, 17, details=True)
+    d = ~same
+    if d.any():
+        first = d & np.concatenate([np.ones_like(same[:, :, :1]), same[:, :, :-1]], axis=2)     # first differing bounce
+        agree_on = (r1["tri"][first] == ref["tri"][first]).mean()
+        agree_off = (r0["tri"][first] == ref["tri"][first]).mean()
+        assert agree_on >= agree_off
+    # the walk is shorter
+    for r in (on, off):
+        r.counters(reset=True)
+        r.trace_paths(1, 3, seed=1, width=128, height=128, flags=ptb.FLAG_COUNT_NODES)
+    c_on, c_off = on.counters(), off.counters()
+    assert c_on["nodes_visited_shadow"] < c_off["nodes_visited_shadow"] and c_on["nodes_visited"] < c_off["nodes_visited"]
+    on.close(); off.close()
+
+
+def test_plane_ids_overflow_disables_culling():
+    """More supporting planes than ids (a random soup): the scene goes without, deterministically."""
+    from test_gpu_soup import soup_scene
+    r = ptb.Renderer(soup_scene(2000, 3), device=0, accel=ptb.ACCEL_LBVH)
+    assert _has_plane_ids(r) == 0
+    r.close()
+    r = ptb.Renderer(soup_scene(120, 3), device=0, accel=ptb.ACCEL_LBVH)
+    assert _has_plane_ids(r) == 1
+    r.close()
