@@ -302,14 +302,14 @@ def run_ours(a):
                 "launches": prof[top][1], "avg_launch_ms": prof[top][0] / max(1, prof[top][1]), "kernel_ms": kernel_ms,
                 "note": "scene lives in shared memory: the kernel is FP32-issue bound, not HBM bound (DESIGN.md)"}
     # DRAM bytes per launch of the dominant kernel: measured per-unit figure from the committed ncu pass
-    # (profiles/r01m_traffic.json; ncu cannot run inside a timed bench) x the units one launch processed here
+    # (profiles/r01r_traffic.json; ncu cannot run inside a timed bench) x the units one launch processed here
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01m_traffic.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01r_traffic.json")))
         key, units = {"bounce_fused": ("bounce_fused", ctr["shaded"]), "shadow": ("shadow_lbvh", ctr["shadow_rays"]),
                       "closest_hit": ("closest_lbvh", ctr["closest_rays"])}.get(roof["kernel"], (None, 0))
         if key and (key == "bounce_fused") == (info["accel"] == "brute") and roof["launches"]:
             roof["traffic"] = tj[key]["dram_bytes_per_unit"] * units / roof["launches"]
-            roof["traffic_source"] = f"profiles/r01m_traffic.json: {tj[key]['dram_bytes_per_unit']} B per {tj[key]['unit']} (ncu dram__bytes_read+write) x units per launch of this run"
+            roof["traffic_source"] = f"profiles/r01r_traffic.json: {tj[key]['dram_bytes_per_unit']} B per {tj[key]['unit']} (ncu dram__bytes_read+write) x units per launch of this run"
             roof["algorithmic_bytes_per_launch"] = bytes_ / roof["launches"]
     except Exception:
         pass
