@@ -592,11 +592,28 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             const double q_n = std::min(2e-10, 8e-9 / (2.0 * std::max(diam, 1e-30))), q_d = 8e-9;
             k_plane_ids<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.verts64, n, q_n, q_d, d_table, d_pid);
             ++g_launches;
-            unsigned long long overflow = 0;
-            cudaMemcpyAsync(&overflow, d_table + PTB_PLANE_IDS + 1, 8, cudaMemcpyDeviceToHost, st);
+            std::vector<unsigned long long> h_table(PTB_PLANE_IDS + 2);
+            cudaMemcpyAsync(h_table.data(), d_table, 8 * (PTB_PLANE_IDS + 2), cudaMemcpyDeviceToHost, st);
             cudaError_t e = cudaStreamSynchronize(st);
-            cudaFreeAsync(d_table, st);
             if (e != cudaSuccess) { ptb_scene_destroy(s); set_error("plane ids: %s", cudaGetErrorString(e)); return PTB_ERR_CUDA; }
+            const bool overflow = h_table[PTB_PLANE_IDS + 1] != 0;
+            if (!overflow) {
+                // the table's slots were handed out in arrival order; renumber the planes by the rank of their keys so
+                // that the ids (they travel in the nodes and in exported hierarchies) do not depend on the race
+                std::vector<unsigned long long> keys_sorted;
+                for (int i = 0; i < PTB_PLANE_IDS; ++i) if (h_table[i]) keys_sorted.push_back(h_table[i]);
+                std::sort(keys_sorted.begin(), keys_sorted.end());
+                unsigned char remap[256];
+                memset(remap, 0, sizeof(remap));
+                for (int i = 0; i < PTB_PLANE_IDS; ++i)
+                    if (h_table[i]) remap[i + 1] = (unsigned char)(1 + (std::lower_bound(keys_sorted.begin(), keys_sorted.end(), h_table[i]) - keys_sorted.begin()));
+                // the table's device memory is free to carry the 256-byte map back (stream-ordered after the read)
+                cudaMemcpyAsync(d_table, remap, 256, cudaMemcpyHostToDevice, st);
+                k_remap_pid<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d_pid, n, (const unsigned char *)d_table);
+                ++g_launches;
+                cudaStreamSynchronize(st);        // `remap` is on the stack
+            }
+            cudaFreeAsync(d_table, st);
             d.tri_pid = overflow ? nullptr : d_pid;      // more planes than ids (a soup): no plane culling for this scene
         }
     } else {

@@ -126,8 +126,14 @@ __global__ void __launch_bounds__(256)
 k_rank_keys(const int *__restrict__ vals, const int *__restrict__ tri_obj, const int *__restrict__ rank, int n, unsigned *__restrict__ keys) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) keys[i] = (unsigned)__ldg(rank + tri_obj[vals[i]]);
 }
+// plane ids as the hash table numbered them (arrival order) -> ranks of the sorted table keys (deterministic)
+__global__ void __launch_bounds__(256)
+k_remap_pid(unsigned char *__restrict__ tri_pid, int n, const unsigned char *__restrict__ remap) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) tri_pid[i] = __ldg(remap + tri_pid[i]);
+}
 // 64-bit hierarchy key of the sorted sequence: object rank above the in-object Morton code, so the radix tree splits
-// objects first (a top level over whole meshes) and each mesh gets its own spatial subtree
+// objects first (a top level over whole meshes) and each mesh gets its own spatial subtree.  (A plane id between the
+// two - one subtree per face of a mesh - was measured: same frame rate, 15.9 against 15.6 shadow nodes per ray.)
 __global__ void __launch_bounds__(256)
 k_key64(const int *__restrict__ vals, const int *__restrict__ tri_obj, const int *__restrict__ rank, const unsigned *__restrict__ morton_orig,
         int n, unsigned long long *__restrict__ key64) {
