@@ -275,6 +275,31 @@ def test_scene_keywords_opt_in(tmp_path, rnd, flat):
     assert Image.open(str(d / "cornell.pnm")).size == (40, 40)
 
 
+def test_scene_per_frame_recycles_memory():
+    """Scenes created and destroyed in a loop take their memory from the stream-ordered pool and share one workspace:
+    device memory in use does not grow, and release_workspace() / ptb_pool_trim give it back."""
+    import torch
+    from pathtracerpython_b200 import synth
+    sc = synth.tessellate(ptb.Scene(ptb.CORNELL_SDL), 12)
+    sc.flatten()
+    used = []
+    first = None
+    for i in range(6):
+        r = ptb.Renderer(sc, device=0, accel=ptb.ACCEL_LBVH)
+        a, _ = r.trace_paths(2, 3, seed=5, width=64, height=64)
+        first = a.clone() if first is None else first
+        assert torch.equal(a, first)                       # same scene, same frame, whatever memory it landed in
+        r.close()
+        torch.cuda.synchronize()
+        free, total = torch.cuda.mem_get_info(0)
+        used.append(total - free)
+    assert max(used[2:]) - min(used[2:]) < (8 << 20), used  # steady state after the pool has warmed up
+    ptb.release_workspace(0)
+    torch.cuda.empty_cache()
+    free2, _ = torch.cuda.mem_get_info(0)
+    assert total - free2 <= used[-1]
+
+
 def test_errors_are_loud(rnd):
     with pytest.raises(ptb.PtbError):
         rnd.trace_paths(1, 1, shard=5, n_shards=2)
