@@ -22,6 +22,12 @@ r.trace_primary(40, 48)
 r.trace_paths(3, 4, seed=2, width=40, height=48)
 r.trace_paths(2, 3, seed=2, width=32, height=32, flags=ptb.FLAG_PHYSICAL)
 r.trace_paths(1, 2, seed=2, width=16, height=16, precision=ptb.PREC_FP64)
+r.trace_paths(1, 2, seed=2, width=16, height=16, flags=ptb.FLAG_COUNT_NODES)
+blob = r.export_bvh()                                # plane ids travel with the hierarchy
+r2 = ptb.Renderer(t, device=0, bvh=blob)
+r2.trace_paths(2, 3, seed=2, width=24, height=24)
+r2.image_scene(r2.trace_paths(1, 1, width=24, height=24)[0], 24, 24)
+r2.close()
 r.close()
 with np.errstate(invalid="ignore", divide="ignore"):
     s = soup_scene(400, 3)
@@ -31,4 +37,5 @@ for accel in (ptb.ACCEL_BRUTE, ptb.ACCEL_LBVH):
     r.trace_primary(32, 32)
     r.trace_paths(2, 3, seed=3, width=32, height=32)
     r.close()
+ptb.release_workspace()
 print("done")
