@@ -136,7 +136,8 @@ int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, dou
 /* Replicating a built scene to other GPUs instead of rebuilding it (the reference pickles the whole scene into
  * every pool task, main.py:199-201, 208-216; here one rank builds and the others receive).
  * ptb_bvh_export copies both hierarchies of an LBVH scene (closest-hit tree over object + light triangles and the
- * occlusion tree over object triangles: 64 B nodes, leaf-ordered 64 B triangle records, slot -> reference index)
+ * occlusion tree over object triangles: 64 B nodes, leaf-ordered 64 B triangle records, slot -> reference index; plus
+ * the per-triangle supporting-plane ids the nodes refer to)
  * into ONE caller-owned device buffer of ptb_bvh_export_bytes(scene) bytes (0 for a scene without LBVH) that can
  * travel through a single broadcast.  ptb_bvh_import is ptb_scene_create with the sort / tree / refit kernels
  * replaced by a device-to-device copy of such a buffer: `desc` must describe the same scene (checked against the

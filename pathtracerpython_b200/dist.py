@@ -58,7 +58,7 @@ def replicate_renderer(scene, device, src=0, group=None, accel=0, make=None):
         try:
             blob = r.export_bvh()
             size[0] = blob.numel()
-        except Exception:           # no LBVH on this scene: everybody builds its own plane list
+        except RuntimeError:        # PtbError "no LBVH": a shared-memory scene, everybody builds its own plane list
             blob = None
     dist.broadcast(size, src=src, group=group)
     n = int(size.item())
