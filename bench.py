@@ -138,6 +138,8 @@ class ClockSampler(threading.Thread):
 
     def summary(self):
         self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=10)      # an nvidia-smi query still in flight holds a driver lock: keep it out of the e2e leg
         sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
