@@ -585,6 +585,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
             if (scene_malloc((void **)&d_pid, (size_t)n, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
             s->allocs.push_back(d_pid);
             if (scene_malloc((void **)&d_table, 8 * (PTB_PLANE_IDS + 2), st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+            s->allocs.push_back(d_table);          // 2 KB, lives with the handle: no error path can leak it
             cudaMemsetAsync(d_table, 0, 8 * (PTB_PLANE_IDS + 2), st);
             // normals within q_n and offsets within q_d: q_n * diameter and q_d stay 4 x below sqrt(1e-5) * 1e-5 = 3.2e-8
             double diam = 0.0;
@@ -613,7 +614,6 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
                 ++g_launches;
                 cudaStreamSynchronize(st);        // `remap` is on the stack
             }
-            cudaFreeAsync(d_table, st);
             d.tri_pid = overflow ? nullptr : d_pid;      // more planes than ids (a soup): no plane culling for this scene
         }
     } else {
