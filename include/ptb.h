@@ -12,6 +12,12 @@
  * them as torch tensors), pointers named h_* / inside ptb_scene_desc are HOST pointers; every
  * launch goes to the caller's CUDA stream (a cudaStream_t passed as void*).  A scene handle is
  * immutable after creation and bound to the device that was current when it was created.
+ *
+ * Threads and devices: any host thread may call in, on any device and stream.  State that CUDA keeps per device
+ * (kernel attributes, the SM count behind the persistent grids, the scene memory pool) is kept per device by the
+ * library; per-call state (work counters, instrumentation switches) lives in the caller's workspace, so two calls
+ * may run at the same time as long as they use different workspaces; ptb_last_error() is per thread.  The profiler
+ * (ptb_profile_*) and the launch counter are process-wide and locked.
  */
 #ifndef PTB_H
 #define PTB_H
@@ -127,11 +133,16 @@ int ptb_version(void);
  * scene (main.py:199-201): uploads the flattened scene and builds the acceleration structure. */
 int ptb_scene_create(const ptb_scene_desc *desc, void *stream, ptb_scene **out);
 int ptb_scene_destroy(ptb_scene *scene);
-/* Scene memory is taken from the device's stream-ordered pool and returns to it on ptb_scene_destroy, so that creating a
- * scene per frame does not pay the driver's allocator each time; ptb_pool_trim hands the pool's unused memory back to
- * the driver (synchronises the device). */
+/* ptb_scene_destroy waits for the streams the handle was used on (not for the device) and frees in stream order.
+ * Scene memory is taken from a stream-ordered pool PRIVATE to the library (one per device; the device's default pool is
+ * left alone) and returns to it on ptb_scene_destroy, so that creating a scene per frame does not pay the driver's
+ * allocator each time.  The pool keeps at most 8 GiB of unused memory across synchronisations; ptb_pool_trim hands
+ * all of it back to the driver (synchronises the device). */
 int ptb_pool_trim(void);
 int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, double *build_ms);
+/* 1 when the scene's hierarchies carry supporting-plane ids (an LBVH scene with at most 255 distinct planes) and the
+ * traversal kernels skip subtrees lying in the plane a ray starts on; 0 otherwise (brute-force scenes, soups). */
+int ptb_scene_plane_culling(const ptb_scene *scene);
 
 /* Replicating a built scene to other GPUs instead of rebuilding it (the reference pickles the whole scene into
  * every pool task, main.py:199-201, 208-216; here one rank builds and the others receive).
@@ -212,6 +223,22 @@ void ptb_obj_free(void *p);
  * leading `# ...` comment. */
 int ptb_obj_write(const char *path, const double *verts, int64_t n_verts, const int64_t *faces, int64_t n_faces,
                   const char *header);
+
+/* 64 B gather peak of the current device (roofline denominator of the LBVH kernels, which are bound by scattered node
+ * and triangle-record fetches, not by DRAM bytes): every lane of a traversal-shaped launch (128 threads, 10 blocks per
+ * SM) chases its own chain of 64 B records - two 256-bit loads, the next index taken from the record just read -
+ * through a buffer of `buffer_bytes`.  64 KB measures L1, 64 MB L2, > 1 GB HBM.  Result in 10^9 fetches per second. */
+int ptb_gather_peak(size_t buffer_bytes, double *gfetch_per_s, void *stream);
+
+/* Known-answer entry for the device functions that have no seam of their own (tier 1).  d_in / d_out are
+ * DEVICE arrays of doubles, n items:
+ *   what 0  rotate about (0,1,0) (main.py:148-162):           in [n][4] = angle, v.xyz           -> out [n][3]
+ *   what 1  pick_random_triangle + sample_random_pt (utils.py:21-46) under the injected Philox stream:
+ *                                                             in [n][4] = pixel, sample, bounce, quad -> out [n][4] = pick, point.xyz
+ *   what 2  make_screen_pts + make_rays (utils.py:55-69):     in [n] = ray index (width, height) -> out [n][3] direction as returned
+ * precision PTB_PREC_FP64: the reference-order flavour; PTB_PREC_FP32: the product's device functions. */
+int ptb_kat(const ptb_scene *scene, int32_t what, int32_t precision, const double *d_in, int64_t n, double *d_out,
+            int32_t width, int32_t height, uint32_t seed, void *stream);
 
 int ptb_counters_read(const ptb_scene *scene, ptb_counters *out, void *stream); /* synchronises stream */
 int ptb_counters_reset(const ptb_scene *scene, void *stream);

@@ -37,6 +37,8 @@ def lib():
         _lib.pto_make_image.restype = C.c_int
         _lib.pto_intersect_one.restype = C.c_int
         _lib.pto_num_threads.restype = C.c_int
+        _lib.pto_set_threads.restype = C.c_int
+        _lib.pto_set_threads.argtypes = [C.c_int]
     return _lib
 
 
@@ -132,3 +134,17 @@ def philox(ctr, key):
 
 def num_threads():
     return lib().pto_num_threads()
+
+
+def host_cores():
+    """Cores this process may run on (cgroup / affinity aware)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def set_threads(n=0):
+    """OpenMP threads of the C restatement; n <= 0: every core this process may use, whatever OMP_NUM_THREADS says
+    (torchrun exports OMP_NUM_THREADS=1 to its children).  Returns the count in force."""
+    return lib().pto_set_threads(int(n) if n > 0 else host_cores())

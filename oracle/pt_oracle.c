@@ -253,85 +253,122 @@ static void rotate_y(double angle, const double *v, double *out) {
     for (int i = 0; i < 3; ++i) out[i] = dot3(R[i], v);   /* np.dot(matrix, v): same fma chain (probed) */
 }
 
+/* one (pixel, sample) path: main.py:186-271 for one value of rays_counter and one pixel.  Outputs indexed
+ * [pixel][sample][bounce] like ref_driver.trace; any output pointer may be NULL.  color = the sample's radiance. */
+static void trace_sample(const pto_scene *sc, int64_t ip, int64_t r, int s, int32_t spp, int32_t bounces, uint32_t seed,
+                         int32_t *tri_out, double *point_out, double *contrib_out, double *k_out,
+                         int8_t *lobe_out, int8_t *occ_out, int8_t *leak_out, double *color,
+                         int64_t *n_closest, int64_t *n_shadow) {
+    double o[3], d[3];
+    primary_ray(sc, r, o, d);
+    double k = 1.0;
+    color[0] = color[1] = color[2] = 0.0;
+    int alive = 1;
+    for (int b = 0; b < bounces; ++b) {
+        size_t idx = ((size_t)ip * spp + s) * bounces + b;
+        if (tri_out) tri_out[idx] = -2;
+        if (lobe_out) lobe_out[idx] = -1;
+        if (occ_out) occ_out[idx] = 0;
+        if (leak_out) leak_out[idx] = -1;
+        if (k_out) k_out[idx] = 0.0;
+        if (point_out) memset(point_out + 3 * idx, 0, 24);
+        if (contrib_out) memset(contrib_out + 3 * idx, 0, 24);
+        if (!alive) continue;
+        double P[3], d2;
+        int t = closest_hit(sc, o, d, P, &d2);
+        (*n_closest)++;
+        if (tri_out) tri_out[idx] = t;
+        if (t < 0) { alive = 0; continue; }
+        if (point_out) memcpy(point_out + 3 * idx, P, 24);
+        int oi = sc->tri_obj[t];
+        const double *nrm = sc->normals + 3 * (size_t)t;
+        double nc[3];
+        if (oi == sc->n_obj) {                      /* light hit: main.py:214-215, 265-266 */
+            for (int i = 0; i < 3; ++i) nc[i] = sc->light_color[i];
+            alive = 0;
+        } else {
+            int occ, leak;
+            compute_color(sc, oi, P, nrm, seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, nc, &occ, &leak);
+            *n_shadow += 3;
+            if (occ_out) occ_out[idx] = (int8_t)occ;
+            if (leak_out) leak_out[idx] = (int8_t)leak;
+        }
+        for (int i = 0; i < 3; ++i) {
+            double cb = nc[i] * k;
+            color[i] = color[i] + cb;               /* main.py:230-231 */
+            if (contrib_out) contrib_out[3 * idx + i] = cb;
+        }
+        if (!alive) { if (k_out) k_out[idx] = k; continue; }
+        /* ---- new ray: main.py:236-268 ---- */
+        const double *m = sc->mat + 8 * (size_t)oi;
+        double kd = m[4], ks = m[5], nexp = m[7];
+        double rnd = uniform_ab(0.0, kd + ks, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 12));
+        double v[3], w[3];
+        double angle = acos(nrm[1]);                /* arccos(dot((0,1,0), normal)) */
+        if (rnd <= kd) {
+            double phi = acos(sqrt(uniform_ab(0, 1, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 13))));
+            double theta = TAU * uniform_ab(0, 1, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 14));
+            v[0] = sin(phi) * cos(theta); v[1] = sin(phi) * sin(theta); v[2] = cos(phi);
+            div3(v, norm3(v));
+            rotate_y(angle, v, w);
+            k *= kd * dot3(w, nrm);
+            if (lobe_out) lobe_out[idx] = 0;
+        } else {
+            double s2 = dot3(nrm, d) * 2;
+            for (int i = 0; i < 3; ++i) v[i] = s2 * nrm[i] - d[i];
+            div3(v, norm3(v));
+            double e[3]; sub3(sc->eye, P, e); div3(e, norm3(e));
+            rotate_y(angle, v, w);
+            k *= ks * pow(dot3(e, w), nexp);
+            if (lobe_out) lobe_out[idx] = 1;
+        }
+        for (int i = 0; i < 3; ++i) { o[i] = P[i]; d[i] = w[i]; }
+        if (k_out) k_out[idx] = k;
+    }
+}
+
 /* full path trace of selected pixels; outputs indexed [pixel][sample][bounce] like ref_driver.trace.
- * Any output pointer except radiance may be NULL. */
+ * Any output pointer except radiance may be NULL.  Threads share the work per pixel when there are many pixels and per
+ * (pixel, sample) when there are few (million-triangle scenes are checked on a few dozen pixels); either way a
+ * pixel's samples are summed in sample order (main.py:269-271), so the result does not depend on the thread count. */
 void pto_trace(const pto_scene *sc, const int64_t *pixels, int64_t n, int32_t spp, int32_t bounces, uint32_t seed,
                int32_t *tri_out, double *point_out, double *contrib_out, double *k_out,
                int8_t *lobe_out, int8_t *occ_out, int8_t *leak_out, double *radiance, int64_t *ray_count) {
     int64_t n_closest = 0, n_shadow = 0;
+    int threads = 1;
+#ifdef _OPENMP
+    threads = omp_get_max_threads();
+#endif
+    if (n >= 64 * (int64_t)threads) {
 #pragma omp parallel for schedule(dynamic, 8) reduction(+ : n_closest, n_shadow)
-    for (int64_t ip = 0; ip < n; ++ip) {
-        int64_t r = pixels ? pixels[ip] : ip;
-        double total[3] = {0, 0, 0};
-        for (int s = 0; s < spp; ++s) {
-            double o[3], d[3];
-            primary_ray(sc, r, o, d);
-            double k = 1.0, color[3] = {0, 0, 0};
-            int alive = 1;
-            for (int b = 0; b < bounces; ++b) {
-                size_t idx = ((size_t)ip * spp + s) * bounces + b;
-                if (tri_out) tri_out[idx] = -2;
-                if (lobe_out) lobe_out[idx] = -1;
-                if (occ_out) occ_out[idx] = 0;
-                if (leak_out) leak_out[idx] = -1;
-                if (k_out) k_out[idx] = 0.0;
-                if (point_out) memset(point_out + 3 * idx, 0, 24);
-                if (contrib_out) memset(contrib_out + 3 * idx, 0, 24);
-                if (!alive) continue;
-                double P[3], d2;
-                int t = closest_hit(sc, o, d, P, &d2);
-                n_closest++;
-                if (tri_out) tri_out[idx] = t;
-                if (t < 0) { alive = 0; continue; }
-                if (point_out) memcpy(point_out + 3 * idx, P, 24);
-                int oi = sc->tri_obj[t];
-                const double *nrm = sc->normals + 3 * (size_t)t;
-                double nc[3];
-                if (oi == sc->n_obj) {                      /* light hit: main.py:214-215, 265-266 */
-                    for (int i = 0; i < 3; ++i) nc[i] = sc->light_color[i];
-                    alive = 0;
-                } else {
-                    int occ, leak;
-                    compute_color(sc, oi, P, nrm, seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, nc, &occ, &leak);
-                    n_shadow += 3;
-                    if (occ_out) occ_out[idx] = (int8_t)occ;
-                    if (leak_out) leak_out[idx] = (int8_t)leak;
-                }
-                for (int i = 0; i < 3; ++i) {
-                    double cb = nc[i] * k;
-                    color[i] = color[i] + cb;               /* main.py:230-231 */
-                    if (contrib_out) contrib_out[3 * idx + i] = cb;
-                }
-                if (!alive) { if (k_out) k_out[idx] = k; continue; }
-                /* ---- new ray: main.py:236-268 ---- */
-                const double *m = sc->mat + 8 * (size_t)oi;
-                double kd = m[4], ks = m[5], nexp = m[7];
-                double rnd = uniform_ab(0.0, kd + ks, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 12));
-                double v[3], w[3];
-                double angle = acos(nrm[1]);                /* arccos(dot((0,1,0), normal)) */
-                if (rnd <= kd) {
-                    double phi = acos(sqrt(uniform_ab(0, 1, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 13))));
-                    double theta = TAU * uniform_ab(0, 1, u01(seed, (uint32_t)r, (uint32_t)s, (uint32_t)b, 14));
-                    v[0] = sin(phi) * cos(theta); v[1] = sin(phi) * sin(theta); v[2] = cos(phi);
-                    div3(v, norm3(v));
-                    rotate_y(angle, v, w);
-                    k *= kd * dot3(w, nrm);
-                    if (lobe_out) lobe_out[idx] = 0;
-                } else {
-                    double s2 = dot3(nrm, d) * 2;
-                    for (int i = 0; i < 3; ++i) v[i] = s2 * nrm[i] - d[i];
-                    div3(v, norm3(v));
-                    double e[3]; sub3(sc->eye, P, e); div3(e, norm3(e));
-                    rotate_y(angle, v, w);
-                    k *= ks * pow(dot3(e, w), nexp);
-                    if (lobe_out) lobe_out[idx] = 1;
-                }
-                for (int i = 0; i < 3; ++i) { o[i] = P[i]; d[i] = w[i]; }
-                if (k_out) k_out[idx] = k;
+        for (int64_t ip = 0; ip < n; ++ip) {
+            int64_t r = pixels ? pixels[ip] : ip;
+            double total[3] = {0, 0, 0};
+            for (int s = 0; s < spp; ++s) {
+                double color[3];
+                trace_sample(sc, ip, r, s, spp, bounces, seed, tri_out, point_out, contrib_out, k_out, lobe_out, occ_out,
+                             leak_out, color, &n_closest, &n_shadow);
+                for (int i = 0; i < 3; ++i) total[i] = total[i] + color[i];   /* main.py:269-271 */
             }
-            for (int i = 0; i < 3; ++i) total[i] = total[i] + color[i];   /* main.py:269-271 */
+            for (int i = 0; i < 3; ++i) radiance[3 * ip + i] = total[i] / (double)spp;   /* main.py:277 */
         }
-        for (int i = 0; i < 3; ++i) radiance[3 * ip + i] = total[i] / (double)spp;   /* main.py:277 */
+    } else {
+        double *colors = (double *)malloc(sizeof(double) * 3 * (size_t)n * (size_t)spp);
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : n_closest, n_shadow)
+        for (int64_t q = 0; q < n * (int64_t)spp; ++q) {
+            int64_t ip = q / spp;
+            int s = (int)(q - ip * spp);
+            int64_t r = pixels ? pixels[ip] : ip;
+            trace_sample(sc, ip, r, s, spp, bounces, seed, tri_out, point_out, contrib_out, k_out, lobe_out, occ_out,
+                         leak_out, colors + 3 * q, &n_closest, &n_shadow);
+        }
+        for (int64_t ip = 0; ip < n; ++ip) {
+            double total[3] = {0, 0, 0};
+            for (int s = 0; s < spp; ++s)
+                for (int i = 0; i < 3; ++i) total[i] = total[i] + colors[3 * (ip * spp + s) + i];
+            for (int i = 0; i < 3; ++i) radiance[3 * ip + i] = total[i] / (double)spp;
+        }
+        free(colors);
     }
     if (ray_count) { ray_count[0] = n_closest; ray_count[1] = n_shadow; }
 }
@@ -357,6 +394,18 @@ int pto_make_image(const double *radiance, int32_t width, int32_t height, uint8_
     for (size_t i = 0; i < 3 * n; ++i) { double v = mat[i] / mx; v = v * 255.0; out[i] = (uint8_t)v; }
     free(mat);
     return 0;
+}
+
+/* bench.py's CPU arm: torchrun exports OMP_NUM_THREADS=1 to its children, which would time one thread and call it
+ * "the host"; n <= 0 leaves the runtime's choice alone.  Returns the thread count now in force. */
+int pto_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    (void)n;
+    return 1;
+#endif
 }
 
 int pto_num_threads(void) {

@@ -14,7 +14,8 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
-           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim"]
+           "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim",
+           "ptb_gather_peak", "ptb_kat", "ptb_scene_plane_culling"]
 
 
 class PtbError(RuntimeError):
@@ -95,6 +96,10 @@ def lib():
         L.ptb_obj_free.restype = None
         L.ptb_obj_write.argtypes = [C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p]
         L.ptb_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+        L.ptb_gather_peak.argtypes = [C.c_size_t, C.POINTER(C.c_double), C.c_void_p]
+        L.ptb_kat.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32,
+                              C.c_uint32, C.c_void_p]
+        L.ptb_scene_plane_culling.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -158,6 +163,13 @@ def profile_read():
     n = (C.c_uint64 * len(PROF_KINDS))()
     check(lib().ptb_profile_read(ms, n), "ptb_profile_read")
     return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(PROF_KINDS)}
+
+
+def gather_peak_gfetch(buffer_bytes):
+    """ptb_gather_peak: dependent random 64 B fetches per second (in 1e9) through a buffer of that size."""
+    v = C.c_double()
+    check(lib().ptb_gather_peak(int(buffer_bytes), C.byref(v), None), "ptb_gather_peak")
+    return float(v.value)
 
 
 def fp32_peak_tflops():

@@ -19,7 +19,46 @@
 namespace ptb {
 
 static thread_local char g_err[512] = "";
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
+std::mutex g_state_mu;
+static DeviceState g_dev[PTB_MAX_DEVICES];
+
+DeviceState *device_state() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    DeviceState *ds = &g_dev[(unsigned)dev < PTB_MAX_DEVICES ? dev : 0];
+    if (!ds->ready.load(std::memory_order_acquire)) {
+        std::lock_guard<std::mutex> lk(g_state_mu);
+        if (!ds->ready.load(std::memory_order_relaxed)) {
+            int sms = 0;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            ds->sms = sms > 0 ? sms : 148;
+            // Scene memory comes from a PRIVATE stream-ordered pool: creating and destroying scenes (a scene per frame,
+            // bench.py's end-to-end step) recycles pool memory instead of going to the driver's allocator (cudaFree
+            // synchronises the device and was measured at 4-240 ms per scene), and the device's default pool - which other
+            // cudaMallocAsync users of the process share - keeps its own release threshold.  The pool holds on to at most
+            // PTB_POOL_KEEP_BYTES of unused memory across synchronisations (a 10 M-triangle scene with its build arena is
+            // 5 GB); ptb_pool_trim hands everything back.
+            ds->pool = nullptr;
+            cudaMemPoolProps props;
+            memset(&props, 0, sizeof(props));
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = dev;
+            cudaMemPool_t pool = nullptr;
+            if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
+                unsigned long long keep = PTB_POOL_KEEP_BYTES;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+                ds->pool = pool;
+            } else {
+                cudaGetLastError();
+            }
+            ds->ready.store(true, std::memory_order_release);
+        }
+    }
+    return ds;
+}
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -28,16 +67,7 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
-static int g_num_sms = 0;
-static int num_sms() {
-    if (!g_num_sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (g_num_sms <= 0) g_num_sms = 148;
-    }
-    return g_num_sms;
-}
+static int num_sms() { return device_state()->sms; }
 // persistent grid: a multiple of the SM count, capped by the work available
 static int grid_for(size_t work, int threads, int blocks_per_sm) {
     size_t need = (work + threads - 1) / threads;
@@ -48,31 +78,35 @@ static int grid_for(size_t work, int threads, int blocks_per_sm) {
 // ---- optional per-kernel-class timing with CUDA events on the launch stream
 enum { PK_GEN = 0, PK_CLOSEST, PK_RETRACE, PK_SHADE, PK_SHADOW, PK_REDUCE, PK_TONEMAP, PK_OTHER, PK_BUILD, PK_SORT, PK_BOUNCE };
 struct ProfRec { int kind; cudaEvent_t a, b; };
-static bool g_prof_on = false;
-static std::vector<ProfRec> g_prof;
-static std::vector<cudaEvent_t> g_event_pool;
+static std::atomic<bool> g_prof_on{false};
+static std::vector<ProfRec> g_prof;             // guarded by g_state_mu (any host thread may be launching)
+static std::vector<cudaEvent_t> g_event_pool;   // guarded by g_state_mu
 static cudaEvent_t prof_event() {
     cudaEvent_t e;
-    if (!g_event_pool.empty()) { e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    {
+        std::lock_guard<std::mutex> lk(g_state_mu);
+        if (!g_event_pool.empty()) { e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    }
     cudaEventCreate(&e);
     return e;
 }
 struct ProfScope {
     bool on; ProfRec r; cudaStream_t st;
-    ProfScope(int kind, cudaStream_t s) : on(g_prof_on), st(s) {
+    ProfScope(int kind, cudaStream_t s) : on(g_prof_on.load(std::memory_order_relaxed)), st(s) {
         if (on) { r.kind = kind; r.a = prof_event(); r.b = prof_event(); cudaEventRecord(r.a, st); }
     }
-    ~ProfScope() { if (on) { cudaEventRecord(r.b, st); g_prof.push_back(r); } }
+    ~ProfScope() { if (on) { cudaEventRecord(r.b, st); std::lock_guard<std::mutex> lk(g_state_mu); g_prof.push_back(r); } }
 };
 
 }  // namespace ptb
 
 using namespace ptb;
 
-extern "C" int ptb_profile_enable(int on) { g_prof_on = on != 0; return PTB_OK; }
+extern "C" int ptb_profile_enable(int on) { g_prof_on.store(on != 0); return PTB_OK; }
 extern "C" int ptb_profile_read(double *ms, uint64_t *launches) {
     PTB_CUDA(cudaDeviceSynchronize());
     for (int i = 0; i < PTB_PROF_KINDS; ++i) { if (ms) ms[i] = 0.0; if (launches) launches[i] = 0; }
+    std::lock_guard<std::mutex> lk(g_state_mu);
     for (ProfRec &r : g_prof) {
         float t = 0.f;
         cudaEventElapsedTime(&t, r.a, r.b);
@@ -84,37 +118,26 @@ extern "C" int ptb_profile_read(double *ms, uint64_t *launches) {
     return PTB_OK;
 }
 
-// Scene memory comes from the device's stream-ordered pool (cudaMallocAsync) with the release threshold lifted, so
-// creating and destroying scenes (a scene per frame, bench.py's end-to-end step) recycles pool memory instead of going
-// to the driver's allocator: cudaFree synchronises the device and was measured at 4-240 ms per scene.
-static int pool_ready_for = -1;
+// Scene memory: the device's private pool (device_state()), plain cudaMallocAsync if the pool could not be created
 static cudaError_t scene_malloc(void **p, size_t bytes, cudaStream_t st) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (pool_ready_for != dev) {
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-            unsigned long long keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-        }
-        pool_ready_for = dev;
-    }
+    DeviceState *ds = device_state();
+    if (ds->pool) return cudaMallocFromPoolAsync(p, std::max<size_t>(bytes, 256), ds->pool, st);
     return cudaMallocAsync(p, std::max<size_t>(bytes, 256), st);
 }
 // ptb_pool_trim (include/ptb.h): hand the pool's unused memory back to the driver
 extern "C" int ptb_pool_trim(void) {
-    int dev = 0;
-    cudaMemPool_t pool;
-    PTB_CUDA(cudaGetDevice(&dev));
+    DeviceState *ds = device_state();
     PTB_CUDA(cudaDeviceSynchronize());
-    PTB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
-    PTB_CUDA(cudaMemPoolTrimTo(pool, 0));
+    if (ds->pool) PTB_CUDA(cudaMemPoolTrimTo(ds->pool, 0));
     return PTB_OK;
 }
 
 struct ptb_scene {
     DScene d;                       // device view handed to kernels by value
     std::vector<void *> allocs;     // device allocations owned by the handle
+    mutable std::mutex mu;          // guards `streams`
+    mutable std::vector<cudaStream_t> streams;   // every stream a call has used the scene on (ptb_scene_destroy waits for them)
+    cudaStream_t create_stream;
     int device;
     float dt_scale;                 // FP32 error scale of the ray parameter (see ptb_isect.cuh)
     double build_ms;
@@ -256,8 +279,6 @@ static size_t lbvh_arena_bytes(int n, int n_objs) {      // upper bound of what 
 static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, const BvhNode **nodes_out, const TriRec **tri_out,
                       const int **ids_out, double *ms_out, void *arena, size_t arena_bytes, cudaStream_t st) {
     DScene &d = s->d;
-    cudaEvent_t e0, e1;
-    cudaEventCreate(&e0); cudaEventCreate(&e1);
     const int n_tiles = (n + PS_TILE - 1) / PS_TILE;
     Aabb *tri_box = nullptr, *node_box = nullptr; float4 *centroid = nullptr; unsigned *scene_box = nullptr, *keys[2] = {nullptr, nullptr};
     int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *node_minref = nullptr; int2 *child = nullptr;
@@ -292,6 +313,12 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
         }
     }
     if (at > arena_bytes) { set_error("LBVH build: arena of %zu bytes, %zu needed", arena_bytes, at); return PTB_ERR_NOMEM; }
+    struct Events {         // destroyed on every way out
+        cudaEvent_t a, b;
+        Events() { cudaEventCreate(&a); cudaEventCreate(&b); }
+        ~Events() { cudaEventDestroy(a); cudaEventDestroy(b); }
+    } ev;
+    const cudaEvent_t e0 = ev.a, e1 = ev.b;
     const unsigned h_n = (unsigned)n;
     cudaMemcpyAsync(d_n, &h_n, sizeof(unsigned), cudaMemcpyHostToDevice, st);
     cudaEventRecord(e0, st);
@@ -366,8 +393,7 @@ static int build_lbvh(ptb_scene *s, int n, int n_objs, const TriRec *src_tri, co
     cudaError_t err = cudaStreamSynchronize(st);
     if (err == cudaSuccess) err = cudaGetLastError();
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (err == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
     if (err != cudaSuccess) { set_error("LBVH build failed: %s", cudaGetErrorString(err)); return PTB_ERR_CUDA; }
     *nodes_out = nodes;
     *tri_out = tri_sorted;    // leaf order
@@ -448,6 +474,8 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     ptb_scene *s = new ptb_scene();
     memset(&s->d, 0, sizeof(DScene));
     cudaGetDevice(&s->device);
+    s->create_stream = (cudaStream_t)stream;
+    s->streams.push_back(s->create_stream);
     const int n = desc->n_tri, no = desc->n_obj;
     // Large scenes (LBVH): the FP64 arrays are uploaded straight from the caller's buffers and the FP32 records,
     // shading normals, scene extent and scale are computed on the device (ptb_bvh_build.cuh); small scenes keep
@@ -463,7 +491,9 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     double *d_ext = nullptr;
     // page-locked landing buffer for the extent pass: a device-to-host copy into pageable memory would block the host
     // until the uploads ahead of it in the stream are done, and the host has tables to compute meanwhile
-    static double *h_ext_pinned = nullptr; static size_t h_ext_cap = 0;
+    struct Pinned { double *p = nullptr; size_t cap = 0; ~Pinned() { if (p) cudaFreeHost(p); } };
+    static thread_local Pinned pinned;       // one per host thread: scenes may be created concurrently
+    double *&h_ext_pinned = pinned.p; size_t &h_ext_cap = pinned.cap;
     struct ExtView { double *p; size_t n; double *data() const { return p; } size_t size() const { return n; } void resize(size_t) {} } h_ext = {nullptr, 0};
     if (dev_records) {      // issue the big uploads and the extent pass; the host tables below are computed while they run
         if ((rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st)) ||
@@ -717,12 +747,14 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
 
 extern "C" int ptb_scene_destroy(ptb_scene *s) {
     if (!s) return PTB_OK;
-    // every stream that used the scene must be done with it before its memory goes back to the pool
+    // every stream that used the scene must be done with it before its memory goes back to the pool: wait for the
+    // streams the handle has seen (not for the whole device - other work of the process keeps running), then free in
+    // the order of the stream the scene was created on
     int cur = 0;
     cudaGetDevice(&cur);
     if (cur != s->device) cudaSetDevice(s->device);
-    cudaDeviceSynchronize();
-    for (void *p : s->allocs) cudaFreeAsync(p, 0);
+    for (cudaStream_t st : s->streams) cudaStreamSynchronize(st);
+    for (void *p : s->allocs) cudaFreeAsync(p, s->create_stream);
     if (cur != s->device) cudaSetDevice(cur);
     delete s;
     return PTB_OK;

@@ -5,8 +5,9 @@ namespace ptb {
 
 // The plane list of a 512-triangle soup (up to 512 records of 96 B) exceeds the 48 KB a kernel gets without asking
 static int planes_optin_smem() {
-    static bool done = false;
-    if (done) return PTB_OK;
+    DeviceState *ds = device_state();      // cudaFuncSetAttribute is per device
+    if (ds->planes_optin.load(std::memory_order_acquire)) return PTB_OK;
+    std::lock_guard<std::mutex> lk(g_state_mu);
     const int bytes = (int)(PTB_BRUTE_MAX_TRI * sizeof(PlaneRec) + 16);
     PTB_CUDA(cudaFuncSetAttribute(k_closest_planes32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     PTB_CUDA(cudaFuncSetAttribute(k_closest_planes32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
@@ -14,7 +15,7 @@ static int planes_optin_smem() {
     PTB_CUDA(cudaFuncSetAttribute(k_shadow_planes_phys32, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    done = true;
+    ds->planes_optin.store(true, std::memory_order_release);
     return PTB_OK;
 }
 
@@ -61,11 +62,15 @@ __global__ void k_cvt_d2f(const double *__restrict__ src, float *__restrict__ ds
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) dst[i] = (float)src[i];
 }
 
-static int check_scene(const ptb_scene *s) {
+static int check_scene(const ptb_scene *s, void *stream = nullptr) {
     if (!s) { set_error("null scene handle"); return PTB_ERR_ARG; }
     int dev = -1;
     cudaGetDevice(&dev);
     if (dev != s->device) { set_error("scene was created on device %d, current device is %d", s->device, dev); return PTB_ERR_ARG; }
+    // remember the stream: ptb_scene_destroy waits for the streams that used the scene, not for the device
+    const cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(s->mu);
+    if (std::find(s->streams.begin(), s->streams.end(), st) == s->streams.end()) s->streams.push_back(st);
     return PTB_OK;
 }
 static int check_pixels(const ptb_pixels *px) {
@@ -79,8 +84,8 @@ static int check_pixels(const ptb_pixels *px) {
 }
 
 static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
-static unsigned g_work_slot = 0;     // rotates through the 32 work counters of a queue set
-static bool g_count_nodes = false;   // instrumented (untimed) run: count nodes visited / triangles tested
+// q.work_slot rotates through the 32 work counters of a queue set; q.count_nodes: instrumented (untimed) run that counts
+// nodes visited / triangles tested.  Both live in the per-call queue set: calls on other streams / threads have their own.
 
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
@@ -90,21 +95,21 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
     if (s->d.accel == PTB_ACCEL_LBVH) {
         const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
         if (s->bvh_dynamic && q.work) {
-            unsigned *work = q.work + (g_work_slot++ & 31);
+            unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (track)
                 k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
-            else if (origin_pid && g_count_nodes)
+            else if (origin_pid && q.count_nodes)
                 k_closest_bvh32_dyn<false, true, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
             else if (origin_pid)
                 k_closest_bvh32_dyn<false, false, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
-            else if (g_count_nodes)
+            else if (q.count_nodes)
                 k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else
                 k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
         } else if (track)
             k_closest_bvh32<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
-        else if (g_count_nodes)
+        else if (q.count_nodes)
             k_closest_bvh32<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
         else
             k_closest_bvh32<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
@@ -123,10 +128,10 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
 }
 
 static int launch_closest64(const ptb_scene *s, const double4 *qo, const double4 *qd, const unsigned *d_count, size_t upper,
-                            double *hit_t, int *hit_tri, cudaStream_t st) {
+                            double *hit_t, int *hit_tri, cudaStream_t st, const int *origin_pid = nullptr) {
     ProfScope ps_(PK_CLOSEST, st);
     if (s->d.accel == PTB_ACCEL_LBVH)
-        k_closest_bvh64<<<grid_for(upper, PTB_BVH_THREADS, 8), PTB_BVH_THREADS, 0, st>>>(s->d, qo, qd, d_count, hit_t, hit_tri);
+        k_closest_bvh64<<<grid_for(upper, PTB_BVH_THREADS, 8), PTB_BVH_THREADS, 0, st>>>(s->d, qo, qd, d_count, hit_t, hit_tri, origin_pid);
     else
         k_closest_brute64<<<grid_for(upper, 128, 8), 128, 0, st>>>(s->d, qo, qd, d_count, hit_t, hit_tri);
     PTB_LAUNCHED();
@@ -143,7 +148,7 @@ extern "C" size_t ptb_trace_primary_workspace(int64_t n_pixels, int32_t precisio
 extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32_t precision, int32_t flags,
                                  int32_t *d_tri, float *d_t, void *d_ws, size_t ws_bytes, void *stream) {
     int rc;
-    if ((rc = check_scene(s)) || (rc = check_pixels(px))) return rc;
+    if ((rc = check_scene(s, stream)) || (rc = check_pixels(px))) return rc;
     if (!d_tri || !d_t || !d_ws) { set_error("ptb_trace_primary: null output/workspace"); return PTB_ERR_ARG; }
     cudaStream_t st = (cudaStream_t)stream;
     BatchInfo bi;
@@ -184,7 +189,7 @@ extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32
 extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t n, int32_t precision,
                                  int32_t *d_tri, void *d_t, void *stream) {
     int rc;
-    if ((rc = check_scene(s))) return rc;
+    if ((rc = check_scene(s, stream))) return rc;
     if (!d_rays || !d_tri || !d_t || n < 0) { set_error("ptb_trace_closest: bad argument"); return PTB_ERR_ARG; }
     if (n == 0) return PTB_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -192,6 +197,7 @@ extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t
     const size_t v = precision == PTB_PREC_FP64 ? sizeof(double4) : sizeof(float4);
     char *scratch = nullptr;
     PTB_CUDA(cudaMallocAsync((void **)&scratch, 2 * v * (size_t)n + 256, st));
+    struct Guard { void *p; cudaStream_t st; ~Guard() { cudaFreeAsync(p, st); } } guard_ = {scratch, st};   // every way out
     unsigned *cnt = (unsigned *)(scratch + 2 * v * (size_t)n);
     if (precision == PTB_PREC_FP32) {
         float4 *qo = (float4 *)scratch, *qd = qo + n;
@@ -210,7 +216,6 @@ extern "C" int ptb_trace_closest(const ptb_scene *s, const void *d_rays, int64_t
         PTB_LAUNCHED();
         if ((rc = launch_closest64(s, qo, qd, cnt, (size_t)n, (double *)d_t, d_tri, st))) return rc;
     }
-    PTB_CUDA(cudaFreeAsync(scratch, st));
     return PTB_OK;
 }
 
@@ -317,20 +322,20 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         }
         { ProfScope ps_(PK_SHADOW, st);
         if (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic) {
-            unsigned *work = q.work + (g_work_slot++ & 31);
+            unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
-            if (origin_pid && g_count_nodes)
+            if (origin_pid && q.count_nodes)
                 k_shadow_bvh32_dyn<true, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
             else if (origin_pid)
                 k_shadow_bvh32_dyn<false, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
-            else if (g_count_nodes)
+            else if (q.count_nodes)
                 k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             else
                 k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             PTB_LAUNCHED();
             k_nee_finish32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
         } else if (d.accel == PTB_ACCEL_LBVH) {
-            if (g_count_nodes)
+            if (q.count_nodes)
                 k_shadow_bvh32<true><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
             else
                 k_shadow_bvh32<false><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);
@@ -371,7 +376,7 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
         const size_t upper = b == 0 ? (size_t)bi.npix : N;
         { ProfScope ps_(PK_CLOSEST, st);
         if (lbvh) {
-            unsigned *work = q.work + (g_work_slot++ & 31);
+            unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             k_closest_bvh32_dyn<false, false, true><<<grid_for(upper, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
                 d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
@@ -403,7 +408,7 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
         }
         { ProfScope ps_(PK_SHADOW, st);
         if (lbvh) {
-            unsigned *work = q.work + (g_work_slot++ & 31);
+            unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             k_shadow_bvh32_dyn<false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
                 d, q.sh_p, q.sh_d, q.count_sh + b, q.sh_res, q.cap, work, nullptr);
@@ -432,14 +437,16 @@ static int run_batch64(const ptb_scene *s, const ptb_render_params *p, Queues<do
     k_gen<double><<<grid_for(N, 256, 8), 256, 0, st>>>(d, bi, q.qo[0], q.qd[0], q.L, q.count, q.unc_count, p->bounces + 2);
     }
     PTB_LAUNCHED();
+    // the plane every live path stands on (same rule as the FP32 pipeline; ptb_bvh_kernels.cuh)
+    int *origin_pid = (d.accel == PTB_ACCEL_LBVH && d.tri_pid) ? q.hit_tri2 : nullptr;
     for (int b = 0; b < p->bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         bi.bounce = b;
-        { int rc2 = launch_closest64(s, q.qo[in], q.qd[in], q.count + b, N, q.hit_t, q.hit_tri, st); if (rc2) return rc2; }
+        { int rc2 = launch_closest64(s, q.qo[in], q.qd[in], q.count + b, N, q.hit_t, q.hit_tri, st, b == 0 ? nullptr : origin_pid); if (rc2) return rc2; }
         { ProfScope ps_(PK_SHADE, st);
         k_shade64<<<grid_for(N, PTB_SHADE_THREADS, 4), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out], q.sh_p, q.sh_d,
-            q.sh_aux, q.L, q.cap, rec);
+            q.sh_aux, q.L, q.cap, rec, origin_pid);
         }
         PTB_LAUNCHED();
         { ProfScope ps_(PK_SHADOW, st);
@@ -469,7 +476,7 @@ extern "C" size_t ptb_trace_paths_workspace(const ptb_render_params *p, int32_t 
 extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
                                float *d_accum, const ptb_path_records *records, void *stream) {
     int rc;
-    if ((rc = check_scene(s))) return rc;
+    if ((rc = check_scene(s, stream))) return rc;
     if (!p || (rc = check_pixels(&p->px))) return rc ? rc : PTB_ERR_ARG;
     if (!d_ws || !d_accum) { set_error("ptb_trace_paths: null workspace/accum"); return PTB_ERR_ARG; }
     if (p->sample_end < p->sample_begin || p->bounces < 0) { set_error("bad sample range / bounces"); return PTB_ERR_ARG; }
@@ -497,7 +504,6 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         if (f64 || rec.any) { set_error("physical mode runs in FP32 and has no reference records"); return PTB_ERR_UNSUPPORTED; }
         if (s->d.accel == PTB_ACCEL_BRUTE && !s->use_planes) { set_error("physical mode needs the plane-grouped records"); return PTB_ERR_UNSUPPORTED; }
     }
-    g_count_nodes = (p->flags & PTB_FLAG_COUNT_NODES) != 0;
     if (rec.any) {
         const size_t n = (size_t)npix * n_samples * p->bounces;
         { ProfScope ps_(PK_OTHER, st);
@@ -510,6 +516,7 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
     Queues<float> q32; Queues<double> q64;
     if (f64) queue_carve<double>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q64);
     else queue_carve<float>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q32);
+    q32.count_nodes = q64.count_nodes = (p->flags & PTB_FLAG_COUNT_NODES) != 0;
     for (int s0 = p->sample_begin; s0 < p->sample_end; s0 += S) {
         bi.S = std::min(S, p->sample_end - s0);
         bi.s_first = s0;
@@ -571,7 +578,7 @@ extern "C" int ptb_scatter_accum(const ptb_pixels *px, const float *d_src, float
 
 extern "C" int ptb_counters_read(const ptb_scene *s, ptb_counters *out, void *stream) {
     int rc;
-    if ((rc = check_scene(s))) return rc;
+    if ((rc = check_scene(s, stream))) return rc;
     if (!out) { set_error("null counters"); return PTB_ERR_ARG; }
     unsigned long long h[CTR_COUNT];
     PTB_CUDA(cudaMemcpyAsync(h, s->d.counters, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
@@ -585,7 +592,7 @@ extern "C" int ptb_counters_read(const ptb_scene *s, ptb_counters *out, void *st
 
 extern "C" int ptb_counters_reset(const ptb_scene *s, void *stream) {
     int rc;
-    if ((rc = check_scene(s))) return rc;
+    if ((rc = check_scene(s, stream))) return rc;
     PTB_CUDA(cudaMemsetAsync(s->d.counters, 0, CTR_COUNT * sizeof(unsigned long long), (cudaStream_t)stream));
     g_launches = 0;
     return PTB_OK;
@@ -627,4 +634,118 @@ extern "C" int ptb_fp32_peak(double *tflops, void *stream) {
     PTB_LAUNCHED();
     *tflops = best;
     return PTB_OK;
+}
+
+// ---------------------------------------------------------------- 64 B gather peak microbenchmark
+// The LBVH kernels are bound by scattered 64 B fetches (two LDG.E.256 per node or triangle record), not by DRAM bytes:
+// at 10^6 triangles the trees sit in L2 and re-ordered rays share L1 lines.  This measures what the memory system
+// delivers for exactly that access: every lane chases its own chain of 64 B records (the next index comes out of the
+// record just loaded, as a child link does) through a buffer of `bytes`, at the traversal kernels' launch shape
+// (128 threads, 10 blocks per SM).  64 KB stays in L1, 64 MB in L2, > 1 GB goes to HBM.
+namespace ptb {
+__global__ void k_gather_fill(uint4 *buf, unsigned n) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint4 h = philox4x32_10(make_uint4(i, 0x9e3779b9u, 0u, 0u), 0x1234567u, 0u);
+        // record = 4 x uint4; the link (next record) sits where BvhNode keeps child 0
+        buf[4 * (size_t)i + 0] = make_uint4(h.y, h.z, h.w, i);
+        buf[4 * (size_t)i + 1] = make_uint4(i, h.y, h.z, h.w);
+        buf[4 * (size_t)i + 2] = make_uint4(h.w, i, h.y, h.z);
+        buf[4 * (size_t)i + 3] = make_uint4(h.x % n, h.w, i, h.y);
+    }
+}
+__global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
+k_gather_chase(const uint4 *__restrict__ buf, unsigned n, int iters, unsigned *out) {
+    unsigned i = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u % n;
+    float acc = 0.f;
+    for (int k = 0; k < iters; ++k) {
+        float4 a, b, c, d;
+        ld256(buf + 4 * (size_t)i, a, b);
+        ld256(buf + 4 * (size_t)i + 2, c, d);
+        acc += a.x + b.y + c.z;                 // every part of the record is consumed
+        i = (unsigned)__float_as_int(d.x);      // dependent: the next address comes out of this record
+    }
+    if (acc == 12345.678f) out[0] = i;
+    if (i == 0xffffffffu) out[1] = 1;
+}
+}  // namespace ptb
+
+extern "C" int ptb_gather_peak(size_t bytes, double *gfetch_per_s, void *stream) {
+    if (!gfetch_per_s || bytes < 4096) { set_error("ptb_gather_peak: bad argument"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned n = (unsigned)std::min<size_t>(bytes / 64, 0x7fffffffu);
+    uint4 *buf = nullptr; unsigned *out = nullptr;
+    PTB_CUDA(cudaMalloc(&buf, (size_t)n * 64 + 64));
+    struct Guard { void *a, *b; ~Guard() { cudaFree(a); if (b) cudaFree(b); } } guard_ = {buf, nullptr};
+    PTB_CUDA(cudaMalloc(&out, 16));
+    guard_.b = out;
+    k_gather_fill<<<num_sms() * 8, 256, 0, st>>>(buf, n);
+    PTB_LAUNCHED();
+    const int grid = num_sms() * PTB_BVH_MIN_BLOCKS, iters = 4096;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(a, st);
+        k_gather_chase<<<grid, PTB_BVH_THREADS, 0, st>>>(buf, n, iters, out);
+        cudaEventRecord(b, st);
+        if (cudaEventSynchronize(b) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        if (rep > 0 && ms > 0.f) best = std::max(best, (double)grid * PTB_BVH_THREADS * iters / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    PTB_LAUNCHED();
+    *gfetch_per_s = best;
+    return PTB_OK;
+}
+
+// ---------------------------------------------------------------- known-answer entry (tier 1)
+namespace ptb {
+__global__ void k_kat(DScene sc, int what, int precision, const double *__restrict__ in, long long n, double *__restrict__ out,
+                      int W, int H, uint32_t seed) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        if (what == 0) {                // rotate(axis (0,1,0), angle, v)   main.py:148-162
+            const double ang = in[4 * i];
+            const d3 v = mk3(in[4 * i + 1], in[4 * i + 2], in[4 * i + 3]);
+            if (precision == PTB_PREC_FP64) {
+                const d3 w = rotate_y64(ang, v);
+                out[3 * i] = w.x; out[3 * i + 1] = w.y; out[3 * i + 2] = w.z;
+            } else {                    // the product derives cos / sin from the normal (bounce32); here from the angle
+                const f3 w = rotate_y32((float)cos(ang), (float)sin(ang), mk3((float)v.x, (float)v.y, (float)v.z));
+                out[3 * i] = w.x; out[3 * i + 1] = w.y; out[3 * i + 2] = w.z;
+            }
+        } else if (what == 1) {         // pick_random_triangle + sample_random_pt   utils.py:21-46
+            const uint4 w = rng4(seed, (uint32_t)in[4 * i], (uint32_t)in[4 * i + 1], (uint32_t)in[4 * i + 2], (uint32_t)in[4 * i + 3]);
+            int li = -1;
+            if (precision == PTB_PREC_FP64) {
+                const d3 p = light_point64(sc, w, li);
+                out[4 * i + 1] = p.x; out[4 * i + 2] = p.y; out[4 * i + 3] = p.z;
+            } else {
+                const f3 p = light_point32(sc, w, li);
+                out[4 * i + 1] = p.x; out[4 * i + 2] = p.y; out[4 * i + 3] = p.z;
+            }
+            out[4 * i] = (double)li;
+        } else {                        // make_screen_pts + make_rays   utils.py:55-69 (direction as returned: not normalised)
+            d3 o, d;
+            primary_ray64(sc, W, H, (int)in[i], o, d);
+            out[3 * i] = d.x; out[3 * i + 1] = d.y; out[3 * i + 2] = d.z;
+        }
+    }
+}
+}  // namespace ptb
+
+extern "C" int ptb_kat(const ptb_scene *s, int32_t what, int32_t precision, const double *d_in, int64_t n, double *d_out,
+                       int32_t width, int32_t height, uint32_t seed, void *stream) {
+    int rc;
+    if ((rc = check_scene(s, stream))) return rc;
+    if (what < 0 || what > 2 || !d_in || !d_out || n < 0 || (precision != PTB_PREC_FP32 && precision != PTB_PREC_FP64)) { set_error("ptb_kat: bad argument"); return PTB_ERR_ARG; }
+    if (what == 2 && (width <= 0 || height <= 0)) { set_error("ptb_kat: width / height"); return PTB_ERR_ARG; }
+    if (n == 0) return PTB_OK;
+    k_kat<<<grid_for((size_t)n, 128, 4), 128, 0, (cudaStream_t)stream>>>(s->d, what, precision, d_in, (long long)n, d_out, width, height, seed);
+    PTB_LAUNCHED();
+    return PTB_OK;
+}
+
+extern "C" int ptb_scene_plane_culling(const ptb_scene *s) {
+    return (s && s->d.accel == PTB_ACCEL_LBVH && s->d.tri_pid) ? 1 : 0;
 }

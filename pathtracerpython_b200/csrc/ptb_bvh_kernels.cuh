@@ -64,7 +64,11 @@ k_shadow_bvh32(DScene sc, const float4 *__restrict__ sh_p, const float4 *__restr
 
 // ---------------------------------------------------------------- FP64 closest hit through the LBVH
 // Exact reference tests at the leaves; boxes are float, padded, so pruning on them is conservative.
-__device__ __forceinline__ Hit64 closest_bvh64(const DScene &sc, d3 pr, d3 dir_in) {
+// opid > 0: supporting-plane id of the triangle the line starts on; children lying wholly in that plane are skipped
+// (ptb_scene.cuh / ptb_bvh_dyn.cuh: the line meets them at t = 0, inside the d^2 > 1e-5 guard).  The FP64 mode runs the
+// same rule as the FP32 product, so its record-for-record equality with the oracle (tests/test_gpu_bvh.py, up to 10^7
+// triangles) is the evidence that the rule changes no outcome.
+__device__ __forceinline__ Hit64 closest_bvh64(const DScene &sc, d3 pr, d3 dir_in, int opid = -1) {
     const d3 vr = xdiv3(dir_in, xnorm(dir_in));
     Hit64 h; h.tri = -1; h.d2 = 0.0; h.P = mk3<double>(0, 0, 0);
     double lim = 1.0e300;
@@ -78,6 +82,7 @@ __device__ __forceinline__ Hit64 closest_bvh64(const DScene &sc, d3 pr, d3 dir_i
         slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
         const double k0 = near_abs(tn0, tf0), k1 = near_abs(tn1, tf1);
         bool go0 = (tn0 <= tf0) && (k0 <= lim), go1 = (tn1 <= tf1) && (k1 <= lim);
+        if (opid > 0) { go0 = go0 && (n.pid0 != opid); go1 = go1 && (n.pid1 != opid); }
         const int c0 = n.d.x, c1 = n.d.y;
 #pragma unroll
         for (int side = 0; side < 2; ++side) {
@@ -104,12 +109,12 @@ __device__ __forceinline__ Hit64 closest_bvh64(const DScene &sc, d3 pr, d3 dir_i
 
 __global__ void __launch_bounds__(PTB_BVH_THREADS)
 k_closest_bvh64(DScene sc, const double4 *__restrict__ qo, const double4 *__restrict__ qd, const unsigned *__restrict__ d_count,
-                double *__restrict__ hit_t, int *__restrict__ hit_tri) {
+                double *__restrict__ hit_t, int *__restrict__ hit_tri, const int *__restrict__ origin_pid = nullptr) {
     const unsigned count = *d_count;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
         const double4 a = qo[i], b = qd[i];
         const d3 pr = mk3(a.x, a.y, a.z), dir = mk3(b.x, b.y, b.z);
-        const Hit64 h = closest_bvh64(sc, pr, dir);
+        const Hit64 h = closest_bvh64(sc, pr, dir, origin_pid ? origin_pid[i] : -1);
         hit_tri[i] = h.tri;
         hit_t[i] = h.tri >= 0 ? xdot(xsub3(h.P, pr), xdiv3(dir, xnorm(dir))) : 0.0;
     }
@@ -117,7 +122,7 @@ k_closest_bvh64(DScene sc, const double4 *__restrict__ qo, const double4 *__rest
 }
 
 // lowest-reference-index occluder (or any, want_min = false) with the reference's FP64 tests
-__device__ __forceinline__ int occluder_bvh64(const DScene &sc, d3 P0, d3 vr, double d2max, bool want_min) {
+__device__ __forceinline__ int occluder_bvh64(const DScene &sc, d3 P0, d3 vr, double d2max, bool want_min, int opid = -1) {
     LineBox<double> lb; lb.set(P0.x, P0.y, P0.z, vr.x, vr.y, vr.z);
     const double lim = sqrt(d2max) * (1.0 + 1e-9) + 1e-9;
     int found = 0x7fffffff;
@@ -130,6 +135,7 @@ __device__ __forceinline__ int occluder_bvh64(const DScene &sc, d3 P0, d3 vr, do
         slab(lb, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w, tn1, tf1);
         bool go0 = (tn0 <= tf0) && (near_abs(tn0, tf0) <= lim) && (n.d.z < found) && (n.d.z < sc.n_tri_obj);
         bool go1 = (tn1 <= tf1) && (near_abs(tn1, tf1) <= lim) && (n.d.w < found) && (n.d.w < sc.n_tri_obj);
+        if (opid > 0) { go0 = go0 && (n.pid0 != opid); go1 = go1 && (n.pid1 != opid); }
         const int c0 = n.d.x, c1 = n.d.y;
 #pragma unroll
         for (int side = 0; side < 2; ++side) {
@@ -167,12 +173,13 @@ k_shadow_bvh64(DScene sc, const double4 *__restrict__ sh_p, const double4 *__res
         const int obj = sc.tri_obj[aux.y];
         double dot_sum = 0.0;
         int occ = 0, leak = sc.n_obj - 1;
+        const int opid = sc.tri_pid ? (int)sc.tri_pid[aux.y] : -1;      // plane of the shaded triangle
 #pragma unroll 1
         for (int s = 0; s < 3; ++s) {
             const double4 dv = sh_d[(size_t)s * cap + j];
             const d3 v = mk3(dv.x, dv.y, dv.z);
             const d3 vr = xdiv3(v, xnorm(v));
-            const int hit = occluder_bvh64(sc, P, vr, dv.w, s == 2);
+            const int hit = occluder_bvh64(sc, P, vr, dv.w, s == 2, opid);
             if (hit >= 0) { occ |= 1 << s; if (s == 2) leak = sc.tri_obj[hit]; }
             else dot_sum = xadd(dot_sum, xdot(v, nrm));
         }

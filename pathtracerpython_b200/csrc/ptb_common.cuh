@@ -6,13 +6,30 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "../../include/ptb.h"
 
 namespace ptb {
 
 // ---------------------------------------------------------------- host-side status
 void set_error(const char *fmt, ...);
-extern unsigned long long g_launches;   // kernels launched by this library (host counter)
+extern std::atomic<unsigned long long> g_launches;   // kernels launched by this library (host counter)
+
+// Per-device state of the library.  include/ptb.h lets any host thread call in on any device and stream, so nothing that
+// CUDA keeps per device (kernel attributes, the SM count, the scene memory pool) may hide behind a process-wide flag.
+#define PTB_MAX_DEVICES 64
+#define PTB_POOL_KEEP_BYTES (8ull << 30)   // unused scene memory the private pool keeps across synchronisations
+struct DeviceState {
+    std::atomic<bool> ready;        // sms / pool filled in
+    int sms;                        // multiprocessor count (persistent grids are multiples of it)
+    std::atomic<bool> sort_optin;   // k_ps_scatter: 64 KB of dynamic shared memory asked for on this device
+    std::atomic<bool> planes_optin; // plane-list kernels: more than 48 KB asked for on this device
+    cudaMemPool_t pool;             // private stream-ordered pool of the scene memory (null: creation failed, plain cudaMallocAsync)
+};
+DeviceState *device_state();        // of the CURRENT device (ptb_api.cu)
+extern std::mutex g_state_mu;       // guards first-use initialisation of a DeviceState and the profiler's lists
 
 #define PTB_CUDA(call)                                                                        \
     do {                                                                                      \

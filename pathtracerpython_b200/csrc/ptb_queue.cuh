@@ -51,6 +51,8 @@ template <typename T> struct Queues {
     unsigned *count_sh;    // physical mode: [bounces + 2] shadow work items per bounce (own compaction)
     SortBufs sort;         // per-bounce re-ordering of the live slots (LBVH scenes, ptb_sort.cuh)
     int cap;               // paths per batch
+    unsigned work_slot;    // host side: next of the 32 `work` counters to hand to a persistent kernel
+    bool count_nodes;      // host side: instrumented run (PTB_FLAG_COUNT_NODES)
 };
 
 template <typename T> inline size_t queue_bytes(size_t cap, int bounces) {
@@ -92,6 +94,7 @@ template <typename T> inline size_t queue_carve(void *ws, size_t bytes, size_t c
     q.count = (unsigned *)take((size_t)(bounces + 4) * sizeof(unsigned));
     q.unc_count = (unsigned *)take(4 * sizeof(unsigned));
     q.cap = (int)cap;
+    q.work_slot = 0; q.count_nodes = false;
     return p <= end ? (size_t)(p - (char *)ws) : 0;
 }
 

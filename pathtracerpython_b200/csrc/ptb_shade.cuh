@@ -103,23 +103,35 @@ __device__ __forceinline__ float pow_small_int(float x, int n) {
 
 // The 3 light samples of one shaded point (main.py:30-40, utils.py:21-46): unit direction to the sampled
 // light point in xyz, squared distance in w.  Philox dims 4s .. 4s+3.
+// One light sample from one Philox quad (utils.py:21-46): area-weighted triangle pick, then the point
+// (c0 v1 + c1 v2 + c2 v3) / (c0 + c1 + c2).  Also the device side of the known-answer entry ptb_kat.
+__device__ __forceinline__ f3 light_point32(const DScene &sc, const uint4 w, int &li) {
+    li = pick_light_int(sc, w.x >> 8);
+    const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
+    const float inv = rcp_approx((c0 + c1) + c2);
+    const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
+    const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
+    return mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)), fmaf(wc, v3.y, fmaf(wb, v2.y, wa * v1.y)),
+               fmaf(wc, v3.z, fmaf(wb, v2.z, wa * v1.z)));
+}
+
 __device__ __forceinline__ void light_samples32(const DScene &sc, uint32_t seed, uint32_t r, uint32_t sample, uint32_t bounce,
                                                 const f3 P, float4 (&out)[3]) {
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const uint4 w = rng4(seed, r, sample, bounce, (uint32_t)s);
-        const int li = pick_light_int(sc, w.x >> 8);
-        const float c0 = u01<float>(w.y), c1 = u01<float>(w.z), c2 = u01<float>(w.w);
-        const float inv = rcp_approx((c0 + c1) + c2);
-        const float wa = c0 * inv, wb = c1 * inv, wc = c2 * inv;
-        const float4 v1 = __ldg(sc.light_v32 + 3 * li), v2 = __ldg(sc.light_v32 + 3 * li + 1), v3 = __ldg(sc.light_v32 + 3 * li + 2);
-        const f3 v = mk3(fmaf(wc, v3.x, fmaf(wb, v2.x, wa * v1.x)) - P.x,
-                         fmaf(wc, v3.y, fmaf(wb, v2.y, wa * v1.y)) - P.y,
-                         fmaf(wc, v3.z, fmaf(wb, v2.z, wa * v1.z)) - P.z);
+        int li;
+        const f3 lp = light_point32(sc, w, li);
+        const f3 v = mk3(lp.x - P.x, lp.y - P.y, lp.z - P.z);
         const float d2 = dot(v, v);
         const float rn = rsqrtf(d2);
         out[s] = make_float4(v.x * rn, v.y * rn, v.z * rn, d2);
     }
+}
+
+// rotate (main.py:148-162) about (0,1,0) by the angle whose cosine / sine are cy / sy
+__device__ __forceinline__ f3 rotate_y32(float cy, float sy, f3 v) {
+    return mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));
 }
 
 // The bounce step (main.py:240-264): lobe pick, new direction wv, new accumulated_k.  Philox dims 12-14.
@@ -141,7 +153,7 @@ __device__ __forceinline__ void bounce32(const DScene &sc, uint32_t seed, uint32
         const float rn = rsqrtf(dot(v, v));
         v = v * rn;
     }
-    wv = mk3(fmaf(cy, v.x, sy * v.z), v.y, fmaf(-sy, v.x, cy * v.z));   // R_y(arccos(n.y)) (main.py:148-162)
+    wv = rotate_y32(cy, sy, v);                                          // R_y(arccos(n.y)) (main.py:148-162)
     if (diffuse) {
         knew = k * (__ldg(sc.mat32 + 8 * obj + 4) * dot(wv, n));
     } else {

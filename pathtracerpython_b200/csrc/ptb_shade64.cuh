@@ -17,11 +17,24 @@ __device__ __forceinline__ d3 rotate_y64(double angle, d3 v) {
     return mk3<double>(__fma_rn(R02, v.z, xmul(R00, v.x)), xmul(R11, v.y), __fma_rn(R22, v.z, xmul(R20, v.x)));
 }
 
+// One light sample in the reference's FP64 operation order (utils.py:21-46, 28-39); also behind ptb_kat
+__device__ __forceinline__ d3 light_point64(const DScene &sc, const uint4 w, int &li) {
+    li = pick_light(sc.light_cdf, sc.n_light_tri, xmul(sc.light_total, u01<double>(w.x)));
+    const double c0 = u01<double>(w.y), c1 = u01<double>(w.z), c2 = u01<double>(w.w);
+    const double sum = xadd(xadd(c0, c1), c2);
+    const double wa = xdiv(c0, sum), wb = xdiv(c1, sum), wc = xdiv(c2, sum);
+    const double *lt = sc.verts64 + 9 * (size_t)(sc.n_tri_obj + li);
+    return mk3<double>(xadd(xadd(xmul(wa, lt[0]), xmul(wb, lt[3])), xmul(wc, lt[6])),
+                       xadd(xadd(xmul(wa, lt[1]), xmul(wb, lt[4])), xmul(wc, lt[7])),
+                       xadd(xadd(xmul(wa, lt[2]), xmul(wb, lt[5])), xmul(wc, lt[8])));
+}
+
 __global__ void __launch_bounds__(PTB_SHADE_THREADS)
 k_shade64(DScene sc, BatchInfo bi, const double4 *__restrict__ qo, const double4 *__restrict__ qd,
           const int *__restrict__ hit_tri, const unsigned *__restrict__ d_count_in, unsigned *d_count_out,
           double4 *__restrict__ qo_out, double4 *__restrict__ qd_out, double4 *__restrict__ sh_p,
-          double4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, double4 *__restrict__ L, int cap, RecPtrs rec) {
+          double4 *__restrict__ sh_d, int2 *__restrict__ sh_aux, double4 *__restrict__ L, int cap, RecPtrs rec,
+          int *__restrict__ origin_pid = nullptr) {
     const unsigned count = *d_count_in;
     const d3 eye = mk3(sc.eye[0], sc.eye[1], sc.eye[2]);
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += gridDim.x * blockDim.x) {
@@ -70,20 +83,15 @@ k_shade64(DScene sc, BatchInfo bi, const double4 *__restrict__ qo, const double4
 
         for (int s = 0; s < 3; ++s) {
             const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);
-            const int li = pick_light(sc.light_cdf, sc.n_light_tri, xmul(sc.light_total, u01<double>(w.x)));
-            const double c0 = u01<double>(w.y), c1 = u01<double>(w.z), c2 = u01<double>(w.w);
-            const double sum = xadd(xadd(c0, c1), c2);
-            const double wa = xdiv(c0, sum), wb = xdiv(c1, sum), wc = xdiv(c2, sum);
-            const double *lt = sc.verts64 + 9 * (size_t)(sc.n_tri_obj + li);
-            const d3 lp = mk3<double>(xadd(xadd(xmul(wa, lt[0]), xmul(wb, lt[3])), xmul(wc, lt[6])),
-                                      xadd(xadd(xmul(wa, lt[1]), xmul(wb, lt[4])), xmul(wc, lt[7])),
-                                      xadd(xadd(xmul(wa, lt[2]), xmul(wb, lt[5])), xmul(wc, lt[8])));
+            int li;
+            const d3 lp = light_point64(sc, w, li);
             d3 v = xsub3(lp, P);
             v = xdiv3(v, xnorm(v));
             sh_d[(size_t)s * cap + j] = make_double4(v.x, v.y, v.z, xsqdist(P, lp));
         }
         sh_p[j] = make_double4(P.x, P.y, P.z, k);
         sh_aux[j] = make_int2(id, tri);
+        if (origin_pid) origin_pid[j] = (int)sc.tri_pid[tri];       // plane the new ray starts on (ptb_bvh_kernels.cuh)
 
         const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, 3u);
         const double *m = sc.mat64 + 8 * obj;

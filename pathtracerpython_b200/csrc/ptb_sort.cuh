@@ -166,8 +166,12 @@ struct SortBufs {
 
 static inline void ps_sort_pass(const unsigned *keys, const unsigned *vals, const unsigned *d_n, int shift, int tiles,
                                 unsigned *ghist, unsigned *totals, unsigned *keys_out, unsigned *vals_out, cudaStream_t st) {
-    static bool once = false;
-    if (!once) { cudaFuncSetAttribute(k_ps_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PS_SCATTER_SMEM); once = true; }
+    DeviceState *ds = device_state();      // the attribute is per device: a second GPU in the same process needs it too
+    if (!ds->sort_optin.load(std::memory_order_acquire)) {
+        std::lock_guard<std::mutex> lk(g_state_mu);
+        cudaFuncSetAttribute(k_ps_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PS_SCATTER_SMEM);
+        ds->sort_optin.store(true, std::memory_order_release);
+    }
     k_ps_hist<<<tiles, PS_WARPS * 32, 0, st>>>(keys, d_n, shift, tiles, ghist);
     k_ps_rowscan<<<256, 1024, 0, st>>>(ghist, tiles, totals);
     k_ps_scatter<<<tiles, PS_WARPS * 32, PS_SCATTER_SMEM, st>>>(keys, vals, d_n, shift, tiles, ghist, totals, keys_out, vals_out);

@@ -280,7 +280,21 @@ class Renderer:
         """-> dict(accel, n_nodes, build_ms) of the device scene."""
         a, n, ms = C.c_int32(), C.c_int32(), C.c_double()
         _lib.check(_lib.lib().ptb_scene_info(self._handle, C.byref(a), C.byref(n), C.byref(ms)), "ptb_scene_info")
-        return {"accel": {1: "brute", 2: "lbvh"}.get(a.value, a.value), "n_nodes": n.value, "build_ms": ms.value}
+        return {"accel": {1: "brute", 2: "lbvh"}.get(a.value, a.value), "n_nodes": n.value, "build_ms": ms.value,
+                "plane_culling": bool(_lib.lib().ptb_scene_plane_culling(self._handle))}
+
+    def kat(self, what, data, precision=_lib.PREC_FP64, width=None, height=None, seed=0):
+        """ptb_kat: known answers of device functions without a seam of their own ("rotate", "light", "ray_dir")."""
+        torch = self.torch
+        code = {"rotate": 0, "light": 1, "ray_dir": 2}[what]
+        x = torch.as_tensor(np.ascontiguousarray(data, np.float64), device=self.device).contiguous()
+        n = x.shape[0]
+        out = torch.empty((n, 4 if code == 1 else 3), dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_kat(self._handle, code, precision, x.data_ptr(), n, out.data_ptr(),
+                                          int(width or self.width), int(height or self.height), int(seed) & 0xFFFFFFFF,
+                                          self._stream()), "ptb_kat")
+        return out.cpu().numpy()
 
     def counters(self, reset=False):
         c = _lib.Counters()
