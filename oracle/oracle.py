@@ -106,6 +106,21 @@ class Oracle:
         out["closest_rays"], out["shadow_rays"] = int(rc[0]), int(rc[1])
         return out
 
+    # ---- known answers (tests/golden/kat_misc.npz)
+    def light_sample(self, seed, positions):
+        """positions [n,4] = (pixel, sample, bounce, light sample index) -> (pick [n], point [n,3])"""
+        pos = np.ascontiguousarray(positions, np.int32).reshape(-1, 4)
+        pick = np.empty(len(pos), np.int32)
+        pt = np.empty((len(pos), 3), np.float64)
+        lib().pto_light_sample(C.byref(self.s), C.c_uint32(seed), _p(pos), C.c_int64(len(pos)), _p(pick), _p(pt))
+        return pick, pt
+
+    def primary_dirs(self, rays):
+        r = np.ascontiguousarray(rays, np.int64)
+        out = np.empty((len(r), 3), np.float64)
+        lib().pto_primary_dirs(C.byref(self.s), _p(r), C.c_int64(len(r)), _p(out))
+        return out
+
     def make_image(self, radiance):
         radiance = np.ascontiguousarray(radiance, np.float64).reshape(-1, 3)
         img = np.empty((self.height, self.width, 3), np.uint8)
@@ -122,6 +137,14 @@ def intersect_one(pr, vr, tri):
     P = np.zeros(3, np.float64)
     hit = lib().pto_intersect_one(_p(pr), _p(vr), _p(tri), _p(P))
     return (P if hit else None)
+
+
+def rotate_y(angles, vecs):
+    a = np.ascontiguousarray(angles, np.float64)
+    v = np.ascontiguousarray(vecs, np.float64).reshape(-1, 3)
+    out = np.empty_like(v)
+    lib().pto_rotate_y(_p(a), _p(v), C.c_int64(len(a)), _p(out))
+    return out
 
 
 def philox(ctr, key):

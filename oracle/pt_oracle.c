@@ -199,24 +199,31 @@ static int pick_random_triangle(const double *areas, int n, double u) {
     return -1;   /* reference returns None */
 }
 
+/* one light sample (main.py:30-34 -> utils.py:21-46) from the injected stream's dims 4s .. 4s+3: the picked light
+ * triangle and the point on it.  Shared by compute_color and the known-answer entry pto_light_sample. */
+static int light_sample(const pto_scene *sc, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce, int s, double *lp) {
+    const double *lverts = sc->verts + 9 * (size_t)sc->n_tri_obj;
+    int li = pick_random_triangle(sc->light_areas, sc->n_light_tri, u01(seed, pixel, sample, bounce, 4 * s));
+    double c0 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 1));
+    double c1 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 2));
+    double c2 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 3));
+    double sum = ((0.0 + c0) + c1) + c2;
+    double a = c0 / sum, b = c1 / sum, c = c2 / sum;
+    const double *lt = lverts + 9 * (size_t)(li < 0 ? 0 : li);
+    for (int i = 0; i < 3; ++i) lp[i] = (a * lt[i] + b * lt[3 + i]) + c * lt[6 + i];
+    return li;
+}
+
 /* main.py:142-145 -> main.py:76-80 + main.py:23-73.  Returns colour; occ/leak are diagnostics. */
 static void compute_color(const pto_scene *sc, int obj_index, const double *point, const double *normal,
                           uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce,
                           double *color, int *occ_out, int *leak_out) {
     const double *m = sc->mat + 8 * (size_t)obj_index;
     double amb[3] = {m[0] * m[3] * sc->ambient, m[1] * m[3] * sc->ambient, m[2] * m[3] * sc->ambient};
-    const double *lverts = sc->verts + 9 * (size_t)sc->n_tri_obj;
     double dot = 0.0; int occ = 0; int leak = sc->n_obj - 1;
     for (int s = 0; s < 3; ++s) {
-        int li = pick_random_triangle(sc->light_areas, sc->n_light_tri, u01(seed, pixel, sample, bounce, 4 * s));
-        double c0 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 1));
-        double c1 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 2));
-        double c2 = uniform_ab(0, 1, u01(seed, pixel, sample, bounce, 4 * s + 3));
-        double sum = ((0.0 + c0) + c1) + c2;
-        double a = c0 / sum, b = c1 / sum, c = c2 / sum;
-        const double *lt = lverts + 9 * (size_t)(li < 0 ? 0 : li);
         double lp[3], v[3];
-        for (int i = 0; i < 3; ++i) lp[i] = (a * lt[i] + b * lt[3 + i]) + c * lt[6 + i];
+        light_sample(sc, seed, pixel, sample, bounce, s, lp);
         sub3(lp, point, v);
         div3(v, norm3(v));
         double light_d2 = squared_dist(point, lp);
@@ -394,6 +401,21 @@ int pto_make_image(const double *radiance, int32_t width, int32_t height, uint8_
     for (size_t i = 0; i < 3 * n; ++i) { double v = mat[i] / mx; v = v * 255.0; out[i] = (uint8_t)v; }
     free(mat);
     return 0;
+}
+
+/* ---------------- known-answer entries (tests/golden/kat_misc.npz, SURVEY.md 4 tier 1) ---------------- */
+/* rotate(axis (0,1,0), angle, v), main.py:148-162 */
+void pto_rotate_y(const double *angle, const double *v, int64_t n, double *out) {
+    for (int64_t i = 0; i < n; ++i) rotate_y(angle[i], v + 3 * i, out + 3 * i);
+}
+/* pick_random_triangle + sample_random_pt (utils.py:21-46) at stream position (pixel, sample, bounce, light sample s) */
+void pto_light_sample(const pto_scene *sc, uint32_t seed, const int32_t *pos /* [n][4] */, int64_t n, int32_t *pick, double *pt) {
+    for (int64_t i = 0; i < n; ++i)
+        pick[i] = light_sample(sc, seed, (uint32_t)pos[4 * i], (uint32_t)pos[4 * i + 1], (uint32_t)pos[4 * i + 2], pos[4 * i + 3], pt + 3 * i);
+}
+/* make_screen_pts + make_rays (utils.py:55-69): direction of ray r as returned (not normalised) */
+void pto_primary_dirs(const pto_scene *sc, const int64_t *rays, int64_t n, double *dirs) {
+    for (int64_t i = 0; i < n; ++i) { double o[3]; primary_ray(sc, rays[i], o, dirs + 3 * i); }
 }
 
 /* bench.py's CPU arm: torchrun exports OMP_NUM_THREADS=1 to its children, which would time one thread and call it

@@ -51,6 +51,28 @@ def tessellate(scene, n):
     return out
 
 
+def warp(scene, amplitude=0.04, freq=2.3):
+    """Scene -> new Scene with every vertex moved by a smooth vector field of its position, p + a * (sin(f p.y + 1),
+    sin(f p.z + 2), sin(f p.x + 3)): shared vertices move together (the meshes stay watertight, the light stays in front
+    of the ceiling), but no two triangles of a tessellated wall lie in one plane any more.  A tessellated + warped
+    Cornell box is the worst case for the LBVH path's supporting-plane culling (10^6 distinct planes: the scene goes
+    without it, ptb_scene_plane_culling == 0) where the flat tessellation (32 planes) is its best case."""
+    def field(v):
+        v = np.asarray(v, np.float64)
+        d = np.stack([np.sin(freq * v[..., 1] + 1.0), np.sin(freq * v[..., 2] + 2.0), np.sin(freq * v[..., 0] + 3.0)], -1)
+        return v + amplitude * d
+
+    out = Scene()
+    for k in ("eye", "width", "height", "ortho", "background", "ambient", "light_color", "npaths", "tonemapping", "seed"):
+        setattr(out, k, getattr(scene, k))
+    out.light_obj = _obj_from_triangles(field(scene.light_obj.triangles), "light")
+    for o in scene.objects:
+        d = dict(o)
+        d["geometry"] = _obj_from_triangles(field(o["geometry"].triangles), "object")
+        out.objects.append(d)
+    return out
+
+
 def write_obj(path, obj):
     """One `v` line per triangle corner and one `f` line per triangle, decimals that read back bit-exactly.  Meshes of
     more than a few thousand triangles go through the library's writer (ptb_obj_write) when it is built."""

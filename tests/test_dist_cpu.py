@@ -1,5 +1,6 @@
 """Host-side multi-GPU logic on CPU: world_size-2 gloo processes check that the tile partition covers
-the frame exactly once and that the single reduce reassembles the full frame on rank 0."""
+the frame exactly once, that the single gather (tile sharding) / reduce (sample sharding) reassembles the full
+frame on rank 0, and the replicate-instead-of-rebuild protocol including its failure path."""
 import os
 import socket
 
@@ -26,15 +27,20 @@ def _worker(rank, world, port, W, H, tile, mode, spp, out):
     full = torch.zeros((W * H, 4), dtype=torch.float32)
     if mode == "tile":
         idx = pdist.shard_ray_indices(W, H, rank, world, tile)
-        # a fake per-pixel "radiance sum" that depends only on the ray index, and the sample count
+        assert len(idx) == pdist.shard_pixel_count(W, H, rank, world, tile)
+        # a fake per-pixel "radiance sum" that depends only on the ray index, and the sample count (pixel-slot order)
         vals = torch.tensor(np.stack([idx, 2 * idx, 3 * idx, np.full_like(idx, spp)], 1), dtype=torch.float32)
-        full[torch.as_tensor(idx)] = vals
+        full.fill_(-1.0)      # the gather must overwrite every pixel: nothing is summed, nothing needs zeroing
+
+        def scatter(g, shard, dst):      # host stand-in for ptb_scatter_accum
+            dst[torch.as_tensor(pdist.shard_ray_indices(W, H, g, world, tile))] = shard
+        pdist.gather_frame(vals, W, H, rank, world, tile, full, scatter)
     else:
         s0, s1 = pdist.sample_range(spp, rank, world)
         r = torch.arange(W * H, dtype=torch.float32)
         full[:, 0] = r * (s1 - s0)
         full[:, 3] = float(s1 - s0)
-    pdist.reduce_frame(full, 0)
+        pdist.reduce_frame(full, 0)
     if rank == 0:
         torch.save(full, out)
     dist.barrier()
@@ -47,11 +53,14 @@ def _run(tmp_path, W, H, tile, mode, spp=5, world=2):
     return torch.load(out)
 
 
-def test_tile_sharding_reduce_gloo(tmp_path):
-    W, H, tile = 37, 11, 5
-    full = _run(tmp_path, W, H, tile, "tile")
-    r = torch.arange(W * H, dtype=torch.float32)
-    assert torch.equal(full[:, 0], r) and torch.equal(full[:, 1], 2 * r) and torch.equal(full[:, 3], torch.full((W * H,), 5.0))
+def test_tile_sharding_gather_gloo(tmp_path):
+    for (W, H, tile) in [(37, 11, 5), (16, 8, 8)]:      # ragged shards (padded gather) and equal ones
+        full = _run(tmp_path, W, H, tile, "tile")
+        r = torch.arange(W * H, dtype=torch.float32)
+        assert torch.equal(full[:, 0], r) and torch.equal(full[:, 1], 2 * r) and torch.equal(full[:, 3], torch.full((W * H,), 5.0))
+    assert pdist.collective_info(1024, 1024, 8, "tile") == {"op": "gather", "bytes": 1024 * 1024 * 16 * 7 // 8,
+                                                            "note": "owned shards to rank 0, float4 per pixel"}
+    assert pdist.collective_info(64, 64, 1, "tile")["bytes"] == 0
 
 
 def test_sample_sharding_reduce_gloo(tmp_path):
@@ -81,6 +90,9 @@ class _FakeRenderer:
         self.scene, self.imported = scene, bvh is not None
         self.blob = bvh if bvh is not None else (torch.arange(scene["n"], dtype=torch.int64) * 7 % 251).to(torch.uint8)
 
+    def info(self):
+        return {"accel": "lbvh" if self.scene["n"] else "brute"}
+
     def export_bvh(self):
         if self.scene["n"] == 0:
             raise RuntimeError("no LBVH")
@@ -95,9 +107,14 @@ def _replicate_worker(rank, world, port, n, out):
 
     def make(scene, device, accel, bvh):
         made.append(bvh is not None)
+        if scene["n"] < 0:
+            raise MemoryError("out of device memory (injected)")
         return _FakeRenderer(scene, bvh)
-    r = pdist.replicate_renderer({"n": n}, "cpu", src=0, make=make)
-    torch.save({"imported": r.imported, "made": made, "blob": r.blob}, f"{out}.{rank}")
+    try:
+        r = pdist.replicate_renderer({"n": n}, "cpu", src=0, make=make)
+        torch.save({"imported": r.imported, "made": made, "blob": r.blob}, f"{out}.{rank}")
+    except Exception as e:      # noqa: BLE001
+        torch.save({"error": type(e).__name__, "made": made}, f"{out}.{rank}")
     dist.barrier()
     dist.destroy_process_group()
 
@@ -112,3 +129,7 @@ def test_replicate_renderer_protocol_gloo(tmp_path):
     mp.spawn(_replicate_worker, args=(2, _free_port(), 0, out), nprocs=2, join=True)
     r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
     assert r0["made"] == [False] and r1["made"] == [False] and not r1["imported"]
+    # the building rank fails: every rank raises (nobody waits in the broadcast), and nobody rebuilds silently
+    mp.spawn(_replicate_worker, args=(2, _free_port(), -1, out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert r0["error"] == "MemoryError" and r1["error"] == "RuntimeError" and r1["made"] == []

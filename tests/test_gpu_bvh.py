@@ -7,9 +7,14 @@ import pathtracerpython_b200 as ptb
 from pathtracerpython_b200 import synth
 from oracle import oracle
 
+from conftest import record_divergence
+
 pytestmark = pytest.mark.gpu
 
 ATOL, RTOL = 1e-4, 1e-3
+# divergent path-bounces of the FP32 LBVH walk against the FP64 oracle (target < 100 ppm on the Cornell geometry; the
+# measured values are printed at the end of the run, conftest.record_divergence)
+LIMIT_LBVH = 1e-3
 
 
 def _sig(rec, ref):
@@ -67,7 +72,7 @@ def test_lbvh_cornell_primary_and_paths_vs_oracle(cornell):
     _, rec = r.trace_paths(3, 4, seed=77, width=96, height=96, records=True)
     rec = _np(rec)
     ok = _sig(rec, ref)
-    assert (~ok & live).sum() / live.sum() < 1e-3
+    assert record_divergence("cornell through the LBVH, 96x96x3spp b4", (~ok & live).sum(), live.sum(), LIMIT_LBVH) < LIMIT_LBVH
     assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
     r.close()
 
@@ -91,7 +96,7 @@ def test_tessellated_2048_vs_oracle(tess8):
     _, rec = r.trace_paths(2, 3, seed=9, width=48, height=48, records=True)
     rec = _np(rec)
     ok = _sig(rec, ref)
-    assert (~ok & live).sum() / live.sum() < 5e-3
+    assert record_divergence("tessellated 2048 triangles, 48x48x2spp b3", (~ok & live).sum(), live.sum(), LIMIT_LBVH) < LIMIT_LBVH
     assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
     r.close()
 
@@ -145,6 +150,52 @@ def test_one_million_triangles_build_and_consistency(cornell):
     acc, _ = r.trace_paths(2, 3, seed=1, width=256, height=256)
     assert bool(np.isfinite(acc.cpu().numpy()).all())
     r.close()
+
+
+def _records_vs_oracle_at_scale(scene, res, n_pixels, spp, nb, seed, label, rng_seed):
+    """Per-path records against the brute-force FP64 oracle (main.py:23-73, 83-122 over ALL the triangles) on a random
+    sample of pixels of the full-size frame: FP64 mode must reproduce every discrete outcome and the contributions to
+    1e-9 - with the supporting-plane culling ACTIVE in the walk, so this is also the evidence that the rule changes
+    no outcome at this size - and the FP32 product must stay within the stated tolerance on matching histories."""
+    flat = scene.flatten()
+    W, H = res
+    r = ptb.Renderer(scene, device=0)
+    assert r.info()["accel"] == "lbvh" and r.info()["plane_culling"]
+    px = np.sort(np.random.default_rng(rng_seed).choice(W * H, n_pixels, replace=False))
+    ref = oracle.Oracle(flat, W, H).trace(spp, nb, seed, pixels=px)
+    live = ref["tri"] > -2
+    assert (ref["tri"][:, :, nb - 1] >= 0).mean() > 0.2                    # paths survive to the last bounce
+    _, rec = r.trace_paths(spp, nb, seed=seed, width=W, height=H, pixel_list=px, precision=ptb.PREC_FP64, records=True)
+    rec = _np(rec)
+    for k in ("tri", "lobe", "occ", "leak"):
+        assert np.array_equal(rec[k], ref[k]), (label, k)
+    assert np.abs(rec["contrib64"] - ref["contrib"]).max() < 1e-9
+    assert np.abs(rec["k_after64"] - ref["k_after"]).max() < 1e-9
+    acc, rec = r.trace_paths(spp, nb, seed=seed, width=W, height=H, pixel_list=px, records=True)
+    rec = _np(rec)
+    ok = _sig(rec, ref)
+    div = record_divergence(label, (~ok & live).sum(), live.sum(), 5e-3)
+    assert div < 5e-3, div
+    assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
+    assert (np.abs(rec["k_after"] - ref["k_after"]) <= ATOL + RTOL * np.abs(ref["k_after"]))[ok].all()
+    # and the radiance the records add up to
+    got = acc[:, :3].cpu().numpy() / spp
+    whole = ok.all(axis=(1, 2))
+    assert (np.abs(got - ref["radiance"]) <= 2e-4 + 2e-3 * np.abs(ref["radiance"]))[whole].all()
+    r.close()
+
+
+def test_one_million_triangles_records_vs_oracle(cornell):
+    """BASELINE.json configs[3]'s scene at its frame size: 1 002 528 triangles, 1024 x 1024, 160 random pixels x 2 spp x
+    3 bounces through the LBVH pipeline (re-ordered rays, plane culling) against the reference's brute-force loops."""
+    _records_vs_oracle_at_scale(synth.tessellate(cornell, 177), (1024, 1024), 160, 2, 3, 33,
+                                "1 002 528 triangles, 160 pixels of 1024x1024 x 2spp b3", 21)
+
+
+def test_ten_million_triangles_records_vs_oracle(cornell):
+    """configs[4]'s scene at its frame size: 9 999 392 triangles, 3840 x 2160, 24 random pixels x 1 spp x 3 bounces."""
+    _records_vs_oracle_at_scale(synth.tessellate(cornell, 559), (3840, 2160), 24, 1, 3, 41,
+                                "9 999 392 triangles, 24 pixels of 3840x2160 x 1spp b3", 22)
 
 
 def test_one_million_triangle_scene_through_the_file_loader(cornell, tmp_path):
@@ -303,20 +354,30 @@ def test_plane_culling_changes_no_outcome(cornell, tess8, monkeypatch):
     off = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
     monkeypatch.delenv("PTB_NO_PLANE_CULL")
     assert _has_plane_ids(on) == 1 and _has_plane_ids(off) == 0
+    assert on.info()["plane_culling"] and not off.info()["plane_culling"]
     a1, r1 = on.trace_paths(3, 4, seed=17, width=96, height=96, records=True)
     a0, r0 = off.trace_paths(3, 4, seed=17, width=96, height=96, records=True)
     r1, r0 = _np(r1), _np(r0)
     same = _sig(r1, r0)
     assert (~same).mean() < 2e-4, (~same).mean()
     assert np.array_equal(r1["contrib"][same], r0["contrib"][same])            # identical arithmetic where histories agree
-    # the culled walk is the one that agrees with the FP64 oracle where the two differ
+    # In FP64 (the reference's arithmetic) the rule must change NOTHING: the culled walk's records equal the unculled
+    # walk's bit for bit, and both equal the brute-force oracle's
     ref = oracle.Oracle(tess8.flatten(), 96, 96).trace(3, 4, 17, details=True)
+    _, q1 = on.trace_paths(3, 4, seed=17, width=96, height=96, precision=ptb.PREC_FP64, records=True)
+    _, q0 = off.trace_paths(3, 4, seed=17, width=96, height=96, precision=ptb.PREC_FP64, records=True)
+    q1, q0 = _np(q1), _np(q0)
+    for k in q1:
+        assert np.array_equal(q1[k], q0[k]), k
+    for k in ("tri", "lobe", "occ", "leak"):
+        assert np.array_equal(q1[k], ref[k]), k
+    assert np.abs(q1["contrib64"] - ref["contrib"]).max() < 1e-9
+    # where the FP32 walks differ, the culled one is the one that agrees with the oracle
     d = ~same
     if d.any():
         first = d & np.concatenate([np.ones_like(same[:, :, :1]), same[:, :, :-1]], axis=2)     # first differing bounce
-        agree_on = (r1["tri"][first] == ref["tri"][first]).mean()
-        agree_off = (r0["tri"][first] == ref["tri"][first]).mean()
-        assert agree_on >= agree_off
+        assert (r1["tri"][first] == ref["tri"][first]).all()
+        assert not (r0["tri"][first] == ref["tri"][first]).any()
     # the walk is shorter
     for r in (on, off):
         r.counters(reset=True)

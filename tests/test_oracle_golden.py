@@ -83,3 +83,25 @@ def test_misc_known_answers(flat):
     kat = g("kat_misc.npz")
     o = oracle.Oracle(flat, 24, 24)
     assert np.array_equal(o.make_image(kat["img_radiance"]), kat["img_u8"])
+    # rotate (main.py:148-162), pick_random_triangle + sample_random_pt (utils.py:21-46), make_rays (utils.py:55-69):
+    # the reference's own outputs for these four functions
+    assert np.abs(oracle.rotate_y(kat["rot_angle"], kat["rot_in"]) - kat["rot_out"]).max() < 1e-14
+    pos = np.array([[pix, 3, 1, 0] for pix in range(len(kat["light_pick"]))], np.int32)
+    pick, pt = oracle.Oracle(flat).light_sample(9, pos)
+    assert np.array_equal(pick, kat["light_pick"])
+    assert np.abs(pt - kat["light_pt"]).max() < 1e-14
+    assert len(set(kat["light_pick"].tolist())) == 2          # both light triangles are drawn
+    dirs = oracle.Oracle(flat, 7, 7).primary_dirs(np.arange(49))
+    assert np.array_equal(dirs, kat["ray_dirs"])              # FP64 linspace, bit for bit
+
+
+def test_trace_does_not_depend_on_how_threads_share_the_work(flat):
+    """pto_trace splits few pixels per (pixel, sample) and many per pixel: same records, same radiance."""
+    o = oracle.Oracle(flat, 64, 64)
+    px = np.arange(100, 110)
+    few = o.trace(3, 3, 5, pixels=px)
+    n = oracle.num_threads()
+    many = o.trace(3, 3, 5, pixels=np.concatenate([px, np.arange(200, 200 + 64 * n)]))
+    for k in ("tri", "lobe", "occ", "leak", "contrib", "k_after", "radiance"):
+        assert np.array_equal(few[k], many[k][:len(px)]), k
+    assert oracle.set_threads(0) == oracle.host_cores()
