@@ -36,7 +36,12 @@ typedef enum {
     PTB_ERR_UNSUPPORTED = -4,
     PTB_ERR_IO = -5,           /* ptb_obj_parse: file cannot be opened / read (the reference: OSError) */
     PTB_ERR_PARSE = -6,        /* ptb_obj_parse: token the reference's float()/int() rejects (ValueError) */
-    PTB_ERR_PARSE_INDEX = -7   /* ptb_obj_parse: blank last line (the reference: IndexError, scene_reader.py:31) */
+    PTB_ERR_PARSE_INDEX = -7,  /* ptb_obj_parse: blank last line (the reference: IndexError, scene_reader.py:31) */
+    PTB_ERR_PARSE_IRREGULAR = -8 /* ptb_obj_parse: input the fast parser leaves to a line-by-line one - a vertex that does not
+                                  have exactly 3 coordinates (the reference keeps any number and raises WrongDimensionError /
+                                  IndexError only when a face mixes or lacks them, vector.py:63-72, 143-146), a face with fewer
+                                  than 3 indices, or a face index outside the vertices read before it (Python wraps negative
+                                  indices and raises IndexError beyond; scene_reader.py:81-83) */
 } ptb_status;
 
 /* Flattened scene = the data the reference keeps in `Scene` / `Obj` objects
@@ -213,7 +218,9 @@ int ptb_fp32_peak(double *tflops, void *stream);
  * about their first vertex, negative = relative indices, 'i/j/k' rejected).  On PTB_OK *verts holds
  * 3*n_verts doubles (bit-identical to Python's float()), *faces 3*n_faces vertex indices, *skipped (may be
  * passed as NULL) the cleaned text of every line with an unknown keyword, '\n'-separated, for the caller to
- * report as the reference does (:102-104).  All three are released with ptb_obj_free.  threads <= 0: all
+ * report as the reference does (:102-104).  Irregular input (PTB_ERR_PARSE_IRREGULAR) and malformed tokens are reported,
+ * not repaired: pathtracerpython_b200.scene.Obj then re-reads the file line by line and raises what the reference
+ * raises for the first offending line (tests/golden/obj_corners.json).  All three are released with ptb_obj_free.  threads <= 0: all
  * host cores.  Pure host code: needs no device. */
 int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts, int64_t **faces, int64_t *n_faces,
                   char **skipped, int threads);

@@ -109,7 +109,7 @@ def check(rc, what):
         raise PtbError(f"{what} failed ({rc}): {lib().ptb_last_error().decode()}")
 
 
-ERR_IO, ERR_PARSE, ERR_PARSE_INDEX = -5, -6, -7
+ERR_IO, ERR_PARSE, ERR_PARSE_INDEX, ERR_PARSE_IRREGULAR = -5, -6, -7, -8
 
 
 def obj_parse(path, threads=0):
@@ -128,6 +128,8 @@ def obj_parse(path, threads=0):
             raise ValueError(msg)
         if rc == ERR_PARSE_INDEX:
             raise IndexError("string index out of range")
+        if rc == ERR_PARSE_IRREGULAR:
+            raise IndexError(msg)           # scene.Obj re-reads such files line by line, with the reference's semantics
         raise PtbError(f"ptb_obj_parse failed ({rc}): {msg}")
     try:
         verts = np.ctypeslib.as_array(C.cast(v, C.POINTER(C.c_double)), (nv.value * 3,)).reshape(-1, 3).copy() \

@@ -14,6 +14,7 @@
 #include "ptb_bvh_kernels.cuh"
 #include "ptb_bvh_dyn.cuh"
 #include "ptb_fused.cuh"
+#include "ptb_fused2.cuh"
 #include "ptb_phys.cuh"
 
 namespace ptb {
@@ -145,6 +146,7 @@ struct ptb_scene {
     PlaneScene planes;              // plane-grouped records (brute-force scenes)
     float pad;                      // LBVH box inflation
     bool use_planes;
+    bool fused_x2;                  // packed-FP32 flavour of the fused per-bounce kernel (ptb_fused2.cuh); PTB_FUSED_X2=0: scalar
     bool bvh_dynamic;               // persistent kernels with dynamic ray fetch (ptb_bvh_dyn.cuh)
     bool sort_rays;                 // per-bounce Morton re-ordering of the live paths (ptb_sort.cuh)
 };
@@ -685,6 +687,7 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     s->planes.n_planes = (int)planes.size(); s->planes.n_occ = n_occ;
     if (accel == PTB_ACCEL_BRUTE && (rc = planes_optin_smem())) { ptb_scene_destroy(s); return rc; }
     s->use_planes = getenv("PTB_BRUTE_V1") == nullptr;
+    { const char *x2 = getenv("PTB_FUSED_X2"); s->fused_x2 = !(x2 && x2[0] == '0'); }
     s->bvh_dynamic = getenv("PTB_BVH_STATIC") == nullptr;
     s->sort_rays = getenv("PTB_NO_SORT") == nullptr;
     s->build_ms = 0.0;

@@ -15,6 +15,10 @@ static int planes_optin_smem() {
     PTB_CUDA(cudaFuncSetAttribute(k_shadow_planes_phys32, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     PTB_CUDA(cudaFuncSetAttribute(k_bounce_planes32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute((k_bounce_planes32x2<true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute((k_bounce_planes32x2<true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute((k_bounce_planes32x2<false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    PTB_CUDA(cudaFuncSetAttribute((k_bounce_planes32x2<false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     ds->planes_optin.store(true, std::memory_order_release);
     return PTB_OK;
 }
@@ -269,7 +273,17 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             bi.bounce = b;
             const int last = b == p->bounces - 1;
             ProfScope ps_(PK_BOUNCE, st);
-            if (b == 0)
+            const int grid_b = grid_for(N, PTB_SHADE_THREADS, 8);
+            if (s->fused_x2) {      // packed FP32 (ptb_fused2.cuh): same results bit for bit, fewer issue slots
+                const float4 *qi = b == 0 ? q.qo[0] : q.qo[in], *di = b == 0 ? q.qd[0] : q.qd[in];
+                const unsigned *cin = q.count + b;
+#define PTB_X2_ARGS d, s->planes, bi, qi, di, ht[in], hr[in], cin, q.count + b + 1, q.qo[out], q.qd[out], ht[out], hr[out], q.L, last, rec
+                if (b == 0 && !last) k_bounce_planes32x2<true, true><<<grid_b, PTB_SHADE_THREADS, smem, st>>>(PTB_X2_ARGS);
+                else if (b == 0) k_bounce_planes32x2<true, false><<<grid_b, PTB_SHADE_THREADS, smem, st>>>(PTB_X2_ARGS);
+                else if (!last) k_bounce_planes32x2<false, true><<<grid_b, PTB_SHADE_THREADS, smem, st>>>(PTB_X2_ARGS);
+                else k_bounce_planes32x2<false, false><<<grid_b, PTB_SHADE_THREADS, smem, st>>>(PTB_X2_ARGS);
+#undef PTB_X2_ARGS
+            } else if (b == 0)
                 k_bounce_planes32<true><<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, smem, st>>>(
                     d, s->planes, bi, q.qo[0], q.qd[0], ht[0], hr[0], q.count, q.count + 1, q.qo[1], q.qd[1], ht[1], hr[1], q.L, last, rec);
             else

@@ -78,7 +78,9 @@ static void parse_slice(Slice *sl) {
         size_t l0 = (size_t)(tok[0].second - tok[0].first);
         if (l0 == 1 && *tok[0].first == 'v') {
             double xyz[3];
-            if (tok.size() < 4) { sl->err = PTB_ERR_PARSE; return; }
+            // the reference keeps however many coordinates the line has and only objects when a face mixes them
+            // (vector.py:63-72): anything but x y z is left to the caller's line-by-line parser
+            if (tok.size() != 4) { sl->err = PTB_ERR_PARSE_IRREGULAR; return; }
             for (size_t i = 1; i < tok.size(); i++) {
                 double d;
                 if (!parse_double(tok[i].first, tok[i].second, &d)) { sl->err = PTB_ERR_PARSE; return; }
@@ -93,7 +95,7 @@ static void parse_slice(Slice *sl) {
                 if (k <= -REL_BIAS / 2 || k >= REL_BIAS) { sl->err = PTB_ERR_PARSE; return; }
                 face.push_back(k < 0 ? k - REL_BIAS : k - 1);
             }
-            if (face.size() < 3) { sl->err = PTB_ERR_PARSE; return; }
+            if (face.size() < 3) { sl->err = PTB_ERR_PARSE_IRREGULAR; return; }
             const int64_t nv = (int64_t)(sl->v.size() / 3);
             for (size_t i = 1; i + 1 < face.size(); i++) {
                 const int64_t tri[3] = {face[0], face[i], face[i + 1]};
@@ -151,20 +153,26 @@ extern "C" int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts,
     int64_t nv = 0, nf = 0;
     size_t nskip = 0;
     for (auto &s : sl) {
-        if (s.err) return fail(s.err, "ptb_obj_parse: malformed 'v' or 'f' line in " + std::string(path));
+        if (s.err) return fail(s.err, (s.err == PTB_ERR_PARSE_IRREGULAR ? "ptb_obj_parse: a 'v' line without exactly 3 coordinates or an 'f' line with fewer than 3 indices in "
+                                                                         : "ptb_obj_parse: malformed 'v' or 'f' line in ") + std::string(path));
         nv += (int64_t)(s.v.size() / 3); nf += (int64_t)(s.f.size() / 3); nskip += s.skipped.size();
     }
     double *V = (double *)malloc(sizeof(double) * (size_t)std::max<int64_t>(nv * 3, 1));
     int64_t *F = (int64_t *)malloc(sizeof(int64_t) * (size_t)std::max<int64_t>(nf * 3, 1));
     char *S = skipped ? (char *)malloc(nskip + 1) : nullptr;
     if (!V || !F || (skipped && !S)) { free(V); free(F); free(S); return fail(PTB_ERR_NOMEM, "ptb_obj_parse: out of host memory"); }
+    std::atomic<int> irregular{0};
     auto stitch = [&](int i, int64_t v0, int64_t f0) {
         Slice &s = sl[(size_t)i];
         if (!s.v.empty()) memcpy(V + v0 * 3, s.v.data(), sizeof(double) * s.v.size());
         for (size_t t = 0; t < s.f_nv.size(); t++)
             for (int c = 0; c < 3; c++) {
                 int64_t k = s.f[t * 3 + c];
-                if (k < -REL_BIAS / 2) k = v0 + s.f_nv[t] + (k + REL_BIAS);   // nv + i, nv = vertices read so far (scene_reader.py:71-72)
+                const int64_t nv_now = v0 + s.f_nv[t];                        // vertices read so far (scene_reader.py:71-72)
+                if (k < -REL_BIAS / 2) k = nv_now + (k + REL_BIAS);           // nv + i
+                // the reference looks the index up among the vertices read SO FAR, with Python's wrap-around for
+                // negatives and IndexError beyond: only plain in-range indices are resolved here
+                if (k < 0 || k >= nv_now) irregular.store(1, std::memory_order_relaxed);
                 F[(f0 + (int64_t)t) * 3 + c] = k;
             }
     };
@@ -179,6 +187,10 @@ extern "C" int ptb_obj_parse(const char *path, double **verts, int64_t *n_verts,
         }
         for (auto &t : th) t.join();
         if (S) S[s0] = 0;
+    }
+    if (irregular.load()) {
+        free(V); free(F); free(S);
+        return fail(PTB_ERR_PARSE_IRREGULAR, "ptb_obj_parse: a face index lies outside the vertices read before it in " + std::string(path));
     }
     *verts = V; *n_verts = nv; *faces = F; *n_faces = nf;
     if (skipped) *skipped = S;

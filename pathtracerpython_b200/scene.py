@@ -36,6 +36,11 @@ def _tokens(line):
     return [t for t in line.split(" ") if t]
 
 
+class WrongDimensionError(Exception):
+    """A face mixes vertices with different numbers of coordinates (the reference: vector.py:7-8, raised by
+    V.__add__, vector.py:63-72, when calc_normal subtracts them, scene_reader.py:5-8)."""
+
+
 def _native_parser_wanted(path, min_bytes):
     import os
     from . import _lib
@@ -59,25 +64,44 @@ class Obj:
         self.path = path
         if native is None:
             native = _native_parser_wanted(path, self.NATIVE_MIN_BYTES)
+        tri_idx = None
         if native:
             from . import _lib
-            self.vertexes, self.faces, skipped = _lib.obj_parse(path)
-            for line in skipped:
-                tok = _tokens(line.replace("\t", " "))
-                print(f"{path}\n\tSkipping command '{tok[0]}' ! \n\tParameters: {tok[1:]}")
-        else:
-            self.vertexes, self.faces = self._parse_python(path)
-        self._finish()
+            try:
+                self.vertexes, self.faces, skipped = _lib.obj_parse(path)
+            except (ValueError, IndexError):
+                # malformed or irregular input (a vertex that does not have 3 coordinates, a face index outside the
+                # vertices read so far, ...): the line-by-line parser below raises exactly what the reference raises,
+                # for the first offending line in file order
+                native = False
+            else:
+                for line in skipped:
+                    tok = _tokens(line.replace("\t", " "))
+                    print(f"{path}\n\tSkipping command '{tok[0]}' ! \n\tParameters: {tok[1:]}")
+        if not native:
+            self.vertexes, self.faces, tri_idx = self._parse_python(path)
+        self._finish(tri_idx, strict=True)
 
     @staticmethod
     def _parse_python(path):
-        verts, faces = [], []
+        """The reference's parser line by line (scene_reader.py:62-104), its failure modes included: vertices keep
+        however many coordinates their line has (vector.py:28-42) and a face is resolved against the vertices read SO
+        FAR with Python's indexing (negative indices wrap, anything else outside raises IndexError); a face whose
+        vertices differ in dimension raises WrongDimensionError (vector.py:63-72), one whose vertices have fewer than 3
+        coordinates IndexError (cross_prod, vector.py:143-146), more than 3 are ignored.  Returns vertexes [n,3] (first
+        three coordinates, missing ones 0), faces as the reference stores them and the resolved vertex index of every
+        triangle corner."""
+        verts, dims, faces, tri_idx = [], [], [], []
         for line in _clean_lines(path):
             tok = _tokens(line)
             if not tok:
                 continue
             if tok[0] == "v":
-                verts.append([float(x) for x in tok[1:]])
+                c = [float(x) for x in tok[1:]]
+                if not c:
+                    raise IndexError("tuple index out of range")            # V([]).coords[0], vector.py:37
+                dims.append(len(c))
+                verts.append((c + [0.0, 0.0])[:3])
             elif tok[0] == "f":
                 nv = len(verts)
                 face = []
@@ -85,13 +109,28 @@ class Obj:
                     i = int(t)                                   # 'i/j/k' -> ValueError, as the reference
                     face.append(nv + i if i < 0 else i - 1)
                 if len(face) > 3:                                # fan about the first vertex (:75-78)
-                    faces.extend((face[0], face[i], face[i + 1]) for i in range(1, len(face) - 1))
+                    new = [(face[0], face[i], face[i + 1]) for i in range(1, len(face) - 1)]
                 else:
-                    faces.append(tuple(face))
+                    new = [tuple(face)]
+                for f in new:
+                    if len(f) < 3:
+                        raise IndexError("list index out of range")          # face[2], scene_reader.py:81-83
+                    r = []
+                    for k in f:
+                        if not -nv <= k < nv:
+                            raise IndexError("list index out of range")      # self.vertexes[face[k]]
+                        r.append(k + nv if k < 0 else k)
+                    if dims[r[1]] != dims[r[0]] or dims[r[2]] != dims[r[0]]:
+                        raise WrongDimensionError(f"Cannot add vectors with dimensions {dims[r[1] if dims[r[1]] != dims[r[0]] else r[2]]} "
+                                                  f"and {dims[r[0]]}")
+                    if dims[r[0]] < 3:
+                        raise IndexError("tuple index out of range")         # u[2] in cross_prod
+                    faces.append(f)
+                    tri_idx.append(r)
             else:
                 print(f"{path}\n\tSkipping command '{tok[0]}' ! \n\tParameters: {tok[1:]}")
-        return (np.asarray([v[:3] for v in verts], np.float64).reshape(-1, 3),
-                np.asarray(faces, np.int64).reshape(-1, 3))
+        return (np.asarray(verts, np.float64).reshape(-1, 3), np.asarray(faces, np.int64).reshape(-1, 3),
+                np.asarray(tri_idx, np.int64).reshape(-1, 3))
 
     @classmethod
     def from_arrays(cls, vertexes, faces, path="<arrays>"):
@@ -102,8 +141,12 @@ class Obj:
         o._finish()
         return o
 
-    def _finish(self):
-        self.triangles = self.vertexes[self.faces] if len(self.faces) else np.zeros((0, 3, 3))
+    def _finish(self, tri_idx=None, strict=False):
+        """tri_idx: resolved vertex index of every triangle corner when it differs from `faces` (the reference stores
+        'f 0 1 2' as (-1, 0, 1) and looks the -1 up among the vertices read so far).  strict (files only): a zero-area
+        triangle raises ZeroDivisionError like the reference's normalize (vector.py:172-173: v * (1 / v.size()))."""
+        idx = self.faces if tri_idx is None else tri_idx
+        self.triangles = self.vertexes[idx] if len(idx) else np.zeros((0, 3, 3))
         a = self.triangles[:, 1] - self.triangles[:, 0]
         b = self.triangles[:, 2] - self.triangles[:, 0]
         cx = a[:, 1] * b[:, 2] - a[:, 2] * b[:, 1]               # vector.py:143-146
@@ -111,6 +154,8 @@ class Obj:
         cz = a[:, 0] * b[:, 1] - a[:, 1] * b[:, 0]
         with np.errstate(all="ignore"):
             size = np.sqrt(cx * cx + cy * cy + cz * cz)          # vector.py:109-111
+            if strict and bool((size == 0.0).any()):
+                raise ZeroDivisionError("float division by zero")
             inv = 1.0 / size                                     # vector.py:172-173: v * (1 / size)
             self.normals = np.stack([cx * inv, cy * inv, cz * inv], axis=1)
         self.areas = size / 2                                    # vector.py:164-165

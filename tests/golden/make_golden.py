@@ -146,8 +146,47 @@ def paths(sc):
                         lobe=r["lobe"], occ=r["occ"], leak=r["leak"], radiance=r["radiance"], image=img)
 
 
+def obj_corners():
+    """The reference's own .obj parser (scene_reader.Obj, unmodified) on every corner case of tests/obj_corners.py:
+    what it returns - vertices as read (any number of coordinates), faces as stored, triangles / normals / areas - or
+    the class of the exception it raises, and how many 'Skipping command' reports it prints."""
+    import contextlib
+    import io
+    import json
+    import tempfile
+    sys.path.insert(0, os.path.dirname(OUT))
+    from obj_corners import CASES
+    _, _, rs = rd.load_reference()
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        for name, text in CASES.items():
+            path = os.path.join(tmp, name + ".obj")
+            with open(path, "w", newline="") as f:
+                f.write(text)
+            buf = io.StringIO()
+            try:
+                with contextlib.redirect_stdout(buf), np.errstate(all="ignore"):
+                    o = rs.Obj(path)
+            except Exception as e:      # noqa: BLE001 - the class is the golden
+                out[name] = {"raises": type(e).__name__}
+                continue
+            out[name] = {"raises": None, "skipped": buf.getvalue().count("Skipping command"),
+                         "vertexes": [[float(c) for c in v.coords] for v in o.vertexes],
+                         "faces": [[int(i) for i in f] for f in o.faces],
+                         "triangles": [[[float(c) for c in list(v.coords)[:3]] for v in t] for t in o.triangles],
+                         "normals": [[float(c) for c in n.coords] for n in o.normals],
+                         "areas": [float(a) for a in o.areas]}
+    with open(os.path.join(OUT, "obj_corners.json"), "w") as f:
+        json.dump(out, f, indent=0)
+    print("obj corner goldens:", {k: v["raises"] or "ok" for k, v in out.items()})
+
+
 if __name__ == "__main__":
+    if "--obj-corners" in sys.argv:      # only the parser goldens (seconds); the rest takes minutes
+        obj_corners()
+        sys.exit(0)
     scene = dump_scene()
+    obj_corners()
     kat_intersect(scene)
     kat_misc(scene)
     primary(scene)

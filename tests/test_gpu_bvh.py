@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 ATOL, RTOL = 1e-4, 1e-3
 # divergent path-bounces of the FP32 LBVH walk against the FP64 oracle (target < 100 ppm on the Cornell geometry; the
 # measured values are printed at the end of the run, conftest.record_divergence)
-LIMIT_LBVH = 1e-3
+LIMIT_LBVH = 1e-4     # measured on B200: 0 and 42 ppm (profiles/r02a_divergence_measured.json)
 
 
 def _sig(rec, ref):
@@ -174,8 +174,9 @@ def _records_vs_oracle_at_scale(scene, res, n_pixels, spp, nb, seed, label, rng_
     acc, rec = r.trace_paths(spp, nb, seed=seed, width=W, height=H, pixel_list=px, records=True)
     rec = _np(rec)
     ok = _sig(rec, ref)
-    div = record_divergence(label, (~ok & live).sum(), live.sum(), 5e-3)
-    assert div < 5e-3, div
+    limit = max(LIMIT_LBVH, 2.5 / live.sum())        # measured 0 on B200; a sample this small gets two flips of slack
+    div = record_divergence(label, (~ok & live).sum(), live.sum(), limit)
+    assert div < limit, div
     assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
     assert (np.abs(rec["k_after"] - ref["k_after"]) <= ATOL + RTOL * np.abs(ref["k_after"]))[ok].all()
     # and the radiance the records add up to

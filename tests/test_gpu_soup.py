@@ -15,6 +15,7 @@ from conftest import record_divergence
 pytestmark = pytest.mark.gpu
 
 ATOL, RTOL = 1e-4, 1e-3
+LIMIT_SOUP = 4e-4      # divergent path-bounces; measured on B200: 0 - 82 ppm (LBVH), 82 ppm (plane list); profiles/r02a_divergence_measured.json
 
 
 def soup_scene(n_tri, seed, n_obj=5, spread=2.2, size=0.9):
@@ -87,7 +88,7 @@ def check_against_oracle(scene, accel, res, spp, nb, seed, max_div32):
 
 @pytest.mark.parametrize("accel", [ptb.ACCEL_BRUTE, ptb.ACCEL_LBVH])
 def test_soup_200_both_back_ends_vs_oracle(accel):
-    check_against_oracle(soup_scene(200, 11), accel, 96, 3, 4, 77, 5e-3)
+    check_against_oracle(soup_scene(200, 11), accel, 96, 3, 4, 77, LIMIT_SOUP)
 
 
 def test_soup_512_planes_fill_shared_memory():
@@ -112,13 +113,13 @@ def test_soup_512_planes_fill_shared_memory():
     rec = _np(rec)
     ok = _sig(rec, ref)
     live = ref["tri"] > -2
-    assert record_divergence("soup 512 planes in shared memory, 32x32x2spp b3", (~ok & live).sum(), live.sum(), 5e-3) < 5e-3
+    assert record_divergence("soup 512 planes in shared memory, 32x32x2spp b3", (~ok & live).sum(), live.sum(), 6e-4) < 6e-4   # 1 of 5897 measured
     assert (np.abs(rec["contrib"] - ref["contrib"]) <= ATOL + RTOL * np.abs(ref["contrib"]))[ok].all()
     r.close()
 
 
 def test_soup_5000_lbvh_vs_oracle():
-    check_against_oracle(soup_scene(5000, 12, n_obj=7, size=0.35), ptb.ACCEL_LBVH, 96, 2, 3, 5, 5e-3)
+    check_against_oracle(soup_scene(5000, 12, n_obj=7, size=0.35), ptb.ACCEL_LBVH, 96, 2, 3, 5, LIMIT_SOUP)
 
 
 def test_soup_back_ends_agree_with_each_other():

@@ -41,41 +41,45 @@ def test_shipped_meshes_parse_identically():
     assert n >= 5
 
 
-GRAMMAR = """# header comment
-   v 0 0 0   # trailing comment
-v\t1.5\t0\t-0.0
-v 1e0 1.25E+1 .5 9.0
-v -3.141592653589793 2.718281828459045e-3 1e-7
-v 0.1 0.2 0.30000000000000004
-v 123456789012345678901234567890 1e308 4.9e-324
-v inf -inf 1e400
-usemtl something red
-f 1 2 3
-f -1 -2 -3
-f 1 2 3 4 5
-\t# tab then comment
-f 0 1 2
+from obj_corners import CASES  # noqa: E402
 
-g group one
-s off
-f +1 -7 3
-"""
+GOLDEN_CORNERS = os.path.join(HERE, "golden", "obj_corners.json")
 
 
-@pytest.mark.filterwarnings("ignore:invalid value")          # the inf vertices, in Obj._finish
-def test_grammar_corners(tmp_path, capsys):
-    p = tmp_path / "g.obj"
-    p.write_text(GRAMMAR)
-    a = Obj(str(p), native=False)
-    out_py = capsys.readouterr().out
-    b = Obj(str(p), native=True)
-    out_c = capsys.readouterr().out
-    same(a, b)
-    assert out_py == out_c and out_py.count("Skipping command") == 3
-    assert a.faces.shape == (7, 3)
-    assert a.faces[1].tolist() == [6, 5, 4]                       # relative to the 7 vertices read so far
-    assert a.faces[5].tolist() == [-1, 0, 1]                      # 'f 0 ..' -> -1, as the reference computes it
-    assert np.isinf(b.vertexes[6]).all()
+@pytest.mark.filterwarnings("ignore:invalid value", "ignore:overflow")          # the inf vertices, in Obj._finish
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_grammar_corners_like_the_reference_parser(tmp_path, capsys, name):
+    """Every corner of the grammar against what the REFERENCE's parser did with the same text
+    (tests/golden/obj_corners.json, written by tests/golden/make_golden.py from the unmodified scene_reader.Obj): the
+    same exception class, or the same vertices (first three coordinates), faces as stored, triangles, normals, areas
+    and number of skipped-command reports - from the line-by-line parser and from ptb_obj_parse."""
+    import json
+    gold = json.load(open(GOLDEN_CORNERS))[name]
+    p = tmp_path / "c.obj"
+    with open(p, "w", newline="") as f:
+        f.write(CASES[name])
+    for native in (False, True):
+        capsys.readouterr()
+        if gold["raises"]:
+            with pytest.raises(Exception) as ei:
+                Obj(str(p), native=native)
+            assert type(ei.value).__name__ == gold["raises"], (native, ei.value)
+            continue
+        o = Obj(str(p), native=native)
+        assert capsys.readouterr().out.count("Skipping command") == gold["skipped"], native
+        want_v = np.array([(v + [0.0, 0.0])[:3] for v in gold["vertexes"]], np.float64).reshape(-1, 3)
+        assert o.vertexes.tobytes() == want_v.tobytes(), native
+        assert o.faces.tolist() == gold["faces"], native
+        for k in ("triangles", "normals", "areas"):
+            want = np.array(gold[k], np.float64).reshape(getattr(o, k).shape)
+            assert np.array_equal(getattr(o, k), want, equal_nan=True), (native, k)      # bit for bit (NaN where the reference has NaN)
+
+
+def test_corner_goldens_cover_every_case():
+    import json
+    gold = json.load(open(GOLDEN_CORNERS))
+    assert set(gold) == set(CASES)
+    assert {g["raises"] for g in gold.values()} >= {None, "WrongDimensionError", "IndexError", "ValueError", "ZeroDivisionError"}
 
 
 def test_crlf_and_missing_final_newline(tmp_path):
@@ -148,6 +152,12 @@ def test_writer_round_trips_every_double(tmp_path):
     v = np.concatenate([rng.standard_normal(3000) * 10.0 ** rng.integers(-30, 30, 3000),
                         np.array([0.0, -0.0, 5e-324, 1.7976931348623157e308, 1e22, 1e23, 0.1, 1 / 3, -1e-5])]).reshape(-1, 3)
     f = rng.integers(0, len(v), (500, 3))
+    # a zero-area face raises ZeroDivisionError when read back, like the reference (vector.py:172-173): keep the others
+    t = v[f]
+    with np.errstate(all="ignore"):
+        size = np.sqrt((np.cross(t[:, 1] - t[:, 0], t[:, 2] - t[:, 0]) ** 2).sum(1))
+    f = f[size != 0.0]
+    assert len(f) > 400
     p = str(tmp_path / "w.obj")
     _lib.obj_write(p, v, f, "round trip")
     for native in (False, True):

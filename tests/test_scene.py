@@ -36,12 +36,18 @@ def test_loader_agrees_with_oracle_port():
 
 def test_obj_grammar(tmp_path, capsys):
     p = tmp_path / "m.obj"
-    p.write_text("# comment\n  v 0 0 0\nv 1 0 0 # trailing\nv\t1 1 0\nv 0 1 0 1.0\n"
+    p.write_text("# comment\n  v 0 0 0\nv 1 0 0 # trailing\nv\t1 1 0\nv 0 1 0\n"
                  "vn 0 0 1\nf 1 2 3 4\nf -4 -3 -2\n\n")
     o = ptb.Obj(str(p))
     assert o.faces.tolist() == [[0, 1, 2], [0, 2, 3], [0, 1, 2]]        # fan + negative indices
     assert np.allclose(o.normals, [[0, 0, 1]] * 3) and np.allclose(o.areas, 0.5)
     assert "Skipping command 'vn'" in capsys.readouterr().out
+    # a 4-coordinate vertex next to 3-coordinate ones: the reference's V.__add__ refuses (vector.py:63-72)
+    from pathtracerpython_b200.scene import WrongDimensionError
+    m = tmp_path / "mixed.obj"
+    m.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0 1.0\nf 1 2 3\n")
+    with pytest.raises(WrongDimensionError):
+        ptb.Obj(str(m))
     q = tmp_path / "slash.obj"
     q.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1/1 2/2 3/3\n")
     with pytest.raises(ValueError):
