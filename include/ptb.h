@@ -62,8 +62,14 @@ typedef struct {
     double ambient;             /* scene.ambient  (scene_reader.py:161) */
     double light_color[3];      /* scene.light_color[:3] (scene_reader.py:164) */
     int32_t accel;              /* PTB_ACCEL_* */
-    int32_t reserved;
+    int32_t reserved;           /* PTB_SCENE_* bits, 0 = none */
 } ptb_scene_desc;
+
+/* ptb_scene_desc.reserved: PTB_SCENE_ARRAYS_ON_DEVICE = `verts`, `normals` and `tri_obj` are DEVICE pointers (the arrays
+ * reached the GPU some other way - e.g. each rank uploads 1/N of them and an all-gather over NVLink completes them,
+ * dist.gather_scene_arrays); the handle copies them device-to-device.  LBVH scenes only; mat and light_areas stay
+ * host pointers (they are small). */
+enum { PTB_SCENE_ARRAYS_ON_DEVICE = 1 };
 
 enum { PTB_ACCEL_AUTO = 0, PTB_ACCEL_BRUTE = 1, PTB_ACCEL_LBVH = 2 };
 
@@ -236,6 +242,10 @@ int ptb_obj_write(const char *path, const double *verts, int64_t n_verts, const 
  * SM) chases its own chain of 64 B records - two 256-bit loads, the next index taken from the record just read -
  * through a buffer of `buffer_bytes`.  64 KB measures L1, 64 MB L2, > 1 GB HBM.  Result in 10^9 fetches per second. */
 int ptb_gather_peak(size_t buffer_bytes, double *gfetch_per_s, void *stream);
+/* The same chase with the records staged in SHARED memory (bytes_per_block of them in each of the 10 blocks per SM;
+ * 1 KB .. 20 KB): the rate a walk would get from tree levels staged there ("why the top of the tree is not
+ * staged"). */
+int ptb_gather_peak_smem(size_t bytes_per_block, double *gfetch_per_s, void *stream);
 
 /* Known-answer entry for the device functions that have no seam of their own (tier 1).  d_in / d_out are
  * DEVICE arrays of doubles, n items:

@@ -8,6 +8,7 @@ LIB_PATH = os.environ.get("PTB_LIB_PATH") or os.path.join(_HERE, "libptb.so")   
 
 PREC_FP32, PREC_FP64 = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
+SCENE_ARRAYS_ON_DEVICE = 1
 FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES, FLAG_PHYSICAL, FLAG_NO_ROULETTE = 1, 2, 4, 8, 16
 
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
@@ -15,7 +16,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_tonemap", "ptb_scatter_accum", "ptb_counters_read", "ptb_counters_reset", "ptb_pixel_count",
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
            "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim",
-           "ptb_gather_peak", "ptb_kat", "ptb_scene_plane_culling"]
+           "ptb_gather_peak", "ptb_gather_peak_smem", "ptb_kat", "ptb_scene_plane_culling"]
 
 
 class PtbError(RuntimeError):
@@ -97,6 +98,7 @@ def lib():
         L.ptb_obj_write.argtypes = [C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p]
         L.ptb_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         L.ptb_gather_peak.argtypes = [C.c_size_t, C.POINTER(C.c_double), C.c_void_p]
+        L.ptb_gather_peak_smem.argtypes = [C.c_size_t, C.POINTER(C.c_double), C.c_void_p]
         L.ptb_kat.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32,
                               C.c_uint32, C.c_void_p]
         L.ptb_scene_plane_culling.argtypes = [C.c_void_p]
@@ -171,6 +173,13 @@ def gather_peak_gfetch(buffer_bytes):
     """ptb_gather_peak: dependent random 64 B fetches per second (in 1e9) through a buffer of that size."""
     v = C.c_double()
     check(lib().ptb_gather_peak(int(buffer_bytes), C.byref(v), None), "ptb_gather_peak")
+    return float(v.value)
+
+
+def gather_peak_smem_gfetch(bytes_per_block=16 << 10):
+    """ptb_gather_peak_smem: the same chase through records staged in shared memory (per block)."""
+    v = C.c_double()
+    check(lib().ptb_gather_peak_smem(int(bytes_per_block), C.byref(v), None), "ptb_gather_peak_smem")
     return float(v.value)
 
 

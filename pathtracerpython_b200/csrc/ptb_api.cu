@@ -161,11 +161,12 @@ template <typename T> static int upload(ptb_scene *s, const std::vector<T> &h, c
     return PTB_OK;
 }
 
-template <typename T> static int upload_raw(ptb_scene *s, const T *src, size_t count, const T **out, cudaStream_t st) {
+template <typename T> static int upload_raw(ptb_scene *s, const T *src, size_t count, const T **out, cudaStream_t st,
+                                            cudaMemcpyKind kind = cudaMemcpyHostToDevice) {
     void *p = nullptr;
     PTB_CUDA(scene_malloc(&p, std::max<size_t>(count, 1) * sizeof(T), st));
     s->allocs.push_back(p);
-    if (count) PTB_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+    if (count) PTB_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), kind, st));
     *out = (const T *)p;
     return PTB_OK;
 }
@@ -483,6 +484,9 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     // shading normals, scene extent and scale are computed on the device (ptb_bvh_build.cuh); small scenes keep
     // the host loop because the plane grouping below needs the records on the host.
     const bool dev_records = accel == PTB_ACCEL_LBVH;
+    const bool dev_arrays = (desc->reserved & PTB_SCENE_ARRAYS_ON_DEVICE) != 0;      // verts / normals / tri_obj are device pointers
+    if (dev_arrays && !dev_records) { delete s; set_error("PTB_SCENE_ARRAYS_ON_DEVICE needs an LBVH scene (small scenes are grouped into planes on the host)"); return PTB_ERR_UNSUPPORTED; }
+    const cudaMemcpyKind up = dev_arrays ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     DScene &d = s->d;
     int rc = PTB_OK;
     double scale = 1.0, blo[3] = {1e300, 1e300, 1e300}, bhi[3] = {-1e300, -1e300, -1e300};
@@ -498,8 +502,8 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     double *&h_ext_pinned = pinned.p; size_t &h_ext_cap = pinned.cap;
     struct ExtView { double *p; size_t n; double *data() const { return p; } size_t size() const { return n; } void resize(size_t) {} } h_ext = {nullptr, 0};
     if (dev_records) {      // issue the big uploads and the extent pass; the host tables below are computed while they run
-        if ((rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st)) ||
-            (rc = upload_raw(s, desc->tri_obj, (size_t)n, &d.tri_obj, st))) { ptb_scene_destroy(s); return rc; }
+        if ((rc = upload_raw(s, desc->verts, (size_t)n * 9, &d.verts64, st, up)) || (rc = upload_raw(s, desc->normals, (size_t)n * 3, &d.normals64, st, up)) ||
+            (rc = upload_raw(s, desc->tri_obj, (size_t)n, &d.tri_obj, st, up))) { ptb_scene_destroy(s); return rc; }
         ext_blocks = grid_for((size_t)n * 3, 256, 4);
         h_ext.n = (size_t)ext_blocks * 8;
         if (h_ext_cap < h_ext.n) {
@@ -519,8 +523,8 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     std::vector<double> mat64((size_t)(no + 1) * 8, 0.0);
     std::copy(desc->mat, desc->mat + (size_t)no * 8, mat64.begin());
     std::vector<float> mat32(mat64.begin(), mat64.end());
-    std::vector<float4> lv((size_t)desc->n_light_tri * 3);
-    for (int i = 0; i < desc->n_light_tri * 3; ++i) {
+    std::vector<float4> lv(dev_arrays ? 0 : (size_t)desc->n_light_tri * 3);
+    for (int i = 0; i < desc->n_light_tri * 3 && !dev_arrays; ++i) {
         const double *p = desc->verts + 9 * (size_t)desc->n_tri_obj + 3 * (size_t)i;
         lv[i] = make_float4((float)p[0], (float)p[1], (float)p[2], 0.f);
     }
@@ -577,8 +581,10 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
     }
     std::vector<unsigned long long> ctr(CTR_COUNT, 0ull);
     std::vector<int> obj_first(no + 2, n);
-    for (int i = n - 1; i >= 0; --i) { const int o = tobj[i]; if ((unsigned)o <= (unsigned)no) obj_first[o] = i; }   // range is checked below
-    for (int k = no; k >= 0; --k) if (obj_first[k] == n && k + 1 <= no + 1) obj_first[k] = obj_first[k + 1];
+    if (!dev_arrays) {
+        for (int i = n - 1; i >= 0; --i) { const int o = tobj[i]; if ((unsigned)o <= (unsigned)no) obj_first[o] = i; }   // range is checked below
+        for (int k = no; k >= 0; --k) if (obj_first[k] == n && k + 1 <= no + 1) obj_first[k] = obj_first[k + 1];
+    }
     pt_.mark("light tables, obj_first (host)");
     if (dev_records) {
         cudaError_t e = cudaStreamSynchronize(st);
@@ -676,6 +682,17 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         (rc = upload(s, light_thr, &d.light_thr, st)) || (rc = upload(s, light_bucket, &d.light_bucket, st)) || (rc = upload(s, lobe_thr, &d.obj_lobe_thr, st)) || (rc = upload(s, pow_int, &d.obj_pow_int, st)) || (rc = upload(s, planes, &s->planes.planes, st)) || (rc = upload(s, ctr, (const unsigned long long **)&d.counters, st))) {
         ptb_scene_destroy(s);
         return rc;
+    }
+    if (dev_arrays) {       // the two tables the host could not derive: computed from the device arrays (ptb_bvh_build.cuh)
+        float4 *d_lv = nullptr;
+        if (scene_malloc((void **)&d_lv, sizeof(float4) * 3 * (size_t)desc->n_light_tri, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(d_lv);
+        k_light_verts32<<<grid_for(3 * (size_t)desc->n_light_tri, 256, 8), 256, 0, st>>>(d.verts64, desc->n_tri_obj, desc->n_light_tri, d_lv);
+        d.light_v32 = d_lv;
+        int *d_first = const_cast<int *>(d.obj_first);          // uploaded above, every entry = n
+        k_obj_first<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>(d.tri_obj, n, no, d_first);
+        k_obj_first_fill<<<1, 32, 0, st>>>(d_first, no, n);
+        g_launches += 3;
     }
     pt_.mark("small uploads");
     d.n_tri = n; d.n_tri_obj = desc->n_tri_obj; d.n_obj = no; d.n_light_tri = desc->n_light_tri;

@@ -713,6 +713,57 @@ extern "C" int ptb_gather_peak(size_t bytes, double *gfetch_per_s, void *stream)
     return PTB_OK;
 }
 
+// The same chase out of SHARED memory: what a block would get from the top levels of a tree staged there (north_star (4):
+// "node and triangle tiles staged in shared memory").  64 B records, four LDS.128 per fetch; random record indices put
+// the lanes of a quarter-warp on the same bank groups, so this is the conflict-laden rate a real walk would see.
+namespace ptb {
+__global__ void __launch_bounds__(PTB_BVH_THREADS, PTB_BVH_MIN_BLOCKS)
+k_gather_chase_smem(const uint4 *__restrict__ buf, unsigned n, int iters, unsigned *out) {
+    extern __shared__ __align__(16) uint4 s_rec[];
+    for (unsigned i = threadIdx.x; i < 4 * n; i += blockDim.x) s_rec[i] = buf[i];
+    __syncthreads();
+    unsigned i = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u % n;
+    float acc = 0.f;
+    for (int k = 0; k < iters; ++k) {
+        const uint4 a = s_rec[4 * i], b = s_rec[4 * i + 1], c = s_rec[4 * i + 2], d = s_rec[4 * i + 3];
+        acc += __uint_as_float(a.x) + __uint_as_float(b.y) + __uint_as_float(c.z);
+        i = d.x;
+    }
+    if (acc == 12345.678f) out[0] = i;
+    if (i == 0xffffffffu) out[1] = 1;
+}
+}  // namespace ptb
+
+extern "C" int ptb_gather_peak_smem(size_t bytes_per_block, double *gfetch_per_s, void *stream) {
+    if (!gfetch_per_s || bytes_per_block < 1024 || bytes_per_block > 20 * 1024) { set_error("ptb_gather_peak_smem: 1 KB .. 20 KB per block (10 blocks per SM)"); return PTB_ERR_ARG; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned n = (unsigned)(bytes_per_block / 64);
+    uint4 *buf = nullptr; unsigned *out = nullptr;
+    PTB_CUDA(cudaMalloc(&buf, (size_t)n * 64 + 64));
+    struct Guard { void *a, *b; ~Guard() { cudaFree(a); if (b) cudaFree(b); } } guard_ = {buf, nullptr};
+    PTB_CUDA(cudaMalloc(&out, 16));
+    guard_.b = out;
+    k_gather_fill<<<num_sms(), 256, 0, st>>>(buf, n);
+    PTB_LAUNCHED();
+    const int grid = num_sms() * PTB_BVH_MIN_BLOCKS, iters = 4096;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(a, st);
+        k_gather_chase_smem<<<grid, PTB_BVH_THREADS, (size_t)n * 64, st>>>(buf, n, iters, out);
+        cudaEventRecord(b, st);
+        if (cudaEventSynchronize(b) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        if (rep > 0 && ms > 0.f) best = std::max(best, (double)grid * PTB_BVH_THREADS * iters / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    PTB_LAUNCHED();
+    *gfetch_per_s = best;
+    return PTB_OK;
+}
+
 // ---------------------------------------------------------------- known-answer entry (tier 1)
 namespace ptb {
 __global__ void k_kat(DScene sc, int what, int precision, const double *__restrict__ in, long long n, double *__restrict__ out,

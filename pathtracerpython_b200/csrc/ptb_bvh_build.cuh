@@ -250,6 +250,31 @@ k_pack(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_b
 
 // Scene extent, max |coordinate| and a tri_obj range check in one pass; every block writes 8 doubles
 // (min xyz, max xyz, max abs, bad-object flag) that the host folds.
+// Scene arrays that are already on the device (PTB_SCENE_ARRAYS_ON_DEVICE): the two small tables the host otherwise
+// derives from its copy - the light's vertices in FP32 (utils.py:41-46 reads them per light sample) and the first
+// triangle of every object (the lowest-occluder rule of the shadow walk) - come from these kernels instead.
+__global__ void __launch_bounds__(256)
+k_light_verts32(const double *__restrict__ verts, int n_tri_obj, int n_light_tri, float4 *__restrict__ out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * n_light_tri; i += gridDim.x * blockDim.x) {
+        const double *p = verts + 9 * (size_t)n_tri_obj + 3 * (size_t)i;
+        out[i] = make_float4((float)p[0], (float)p[1], (float)p[2], 0.f);
+    }
+}
+__global__ void __launch_bounds__(256)
+k_obj_first(const int *__restrict__ tri_obj, int n, int n_obj, int *__restrict__ first) {      // first[] preset to n
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int o = tri_obj[i];
+        // triangles are listed object by object (ptb_scene_desc): only the first of a run needs the atomic
+        if ((unsigned)o <= (unsigned)n_obj && (i == 0 || tri_obj[i - 1] != o)) atomicMin(first + o, i);
+    }
+}
+__global__ void k_obj_first_fill(int *first, int n_obj, int n) {      // empty objects take their successor's first triangle
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        first[n_obj + 1] = n;
+        for (int k = n_obj; k >= 0; --k) if (first[k] == n) first[k] = first[k + 1];
+    }
+}
+
 __global__ void __launch_bounds__(256)
 k_scene_extent(const double *__restrict__ verts, size_t n_pts, const int *__restrict__ tri_obj, int n_tri, int n_obj, double *__restrict__ out) {
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, mx = 0.0, bad = 0.0;

@@ -41,6 +41,14 @@ namespace ptb {
 #ifndef PTB_SHADOW_GROUP
 #define PTB_SHADOW_GROUP 32
 #endif
+// closest-hit kernel: one pending-leaf slot per lane.  A leaf child is parked in the slot instead of being tested on the
+// spot; the triangle block runs for the whole warp when some lane needs its slot a second time (or finishes its ray with
+// the slot occupied) - about every tenth node step with half the lanes taking part, instead of two steps out of three
+// with one or two lanes (a lane meets a leaf in 7 % of its node steps, a 16-lane warp in 69 % of them).  Costs: the hit is
+// known a few steps later, so the pruning bound shrinks later and a ray visits a few more nodes (counted: PTB_FLAG_COUNT_NODES).
+#ifndef PTB_CLOSEST_DEFER
+#define PTB_CLOSEST_DEFER 0
+#endif
 #define PTB_WW_DONE ((int)0x80000000)   // traversal state: nothing left (leaf codes are ~slot > INT_MIN)
 
 // warp-wide claim of new work items for the lanes with want == true; returns the claimed index or
@@ -70,7 +78,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
     const unsigned count = *d_count;
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
-    int sp = 0, node = 0, best_ref = 0x7fffffff, opid = -1;
+    int sp = 0, node = 0, best_ref = 0x7fffffff, opid = -1, pend = 0;
     unsigned ray = 0xffffffffu;
     bool exhausted = false;                 // warp-uniform: the pool ran dry
     Hit32 h; h.t = 0.f; h.abs_t = 0.f; h.slot = -1;
@@ -88,7 +96,7 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
                 h.t = 0.f; h.abs_t = 3.0e38f; h.slot = -1; best_ref = 0x7fffffff;
                 uc.init();
-                sp = 0; node = 0;
+                sp = 0; node = 0; pend = 0;
                 if (PID) { const int pr = origin_pid[ray]; opid = pr ? pr : -1; }
             }
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
@@ -110,36 +118,62 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 go1 = go1 && (far_abs(tn1, tf1) >= PTB_TMIN_SAFE);
             }
             if (PID) { go0 = go0 && (n.pid0 != opid); go1 = go1 && (n.pid1 != opid); }
-            // leaf children: one shared test block walked up to twice, so lanes with a single leaf child (either side)
-            // run it together instead of the warp stepping through a copy per side
-            const bool leaf0 = go0 && c0 < 0, leaf1 = go1 && c1 < 0;
-            int lc = leaf0 ? c0 : c1, lref = leaf0 ? m0 : m1;
-            int n_leaf = (leaf0 ? 1 : 0) + (leaf1 ? 1 : 0);
-#pragma unroll 1
-            while (n_leaf > 0) {
-                const int slot = ~lc;
-                const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
-                float4 q0, q1, q2, q3;
-                ld256(tp, q0, q1);
-                if (TRACK) ld256(tp + 2, q2, q3); else q2 = __ldg(tp + 2);
-                const float eps = TRACK ? q3.x : 0.f;
-                if (COUNT) nt++;
-                float t, dt = 0.f; bool edge = false;
-                const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
-                const int ref = lref;                      // leaf: the min-ref field is the triangle itself
-                const float a = fabsf(t);
-                const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
-                if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
-                    if (TRACK) {
-                        if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
-                        uc.best_dt = dt; uc.best_edge = edge;
+            if (PTB_CLOSEST_DEFER && !TRACK) {
+                int l0 = (go0 && c0 < 0) ? c0 : 0, l1 = (go1 && c1 < 0) ? c1 : 0;      // incoming leaves (codes are < 0)
+                if (pend == 0) { if (l0) { pend = l0; l0 = 0; } else { pend = l1; l1 = 0; } }
+                // this step ends the ray when nothing is left to descend into or pop: its parked leaf must be tested first
+                const bool ending = !((go0 && c0 >= 0) || (go1 && c1 >= 0)) && sp == 0;
+                bool overflow = ((l0 | l1) != 0) || (ending && pend != 0);
+                while (__any_sync(__activemask(), overflow)) {
+                    if (pend) {
+                        const int slot = ~pend;
+                        const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
+                        float4 q0, q1, q2, q3;
+                        ld256(tp, q0, q1); ld256(tp + 2, q2, q3);
+                        if (COUNT) nt++;
+                        float t, dt = 0.f; bool edge = false;
+                        const bool hit = tri_test32<false>(q0, q1, q2, 0.f, o, d, dt_scale, t, edge, dt);
+                        const int ref = __float_as_int(q3.w);
+                        const float a = fabsf(t);
+                        const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
+                        if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) { h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref; }
+                        pend = 0;
                     }
-                    h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref;
-                } else if (TRACK && (hit || edge)) {
-                    uc.comp_lo = fminf(uc.comp_lo, a - dt);
+                    if (l0) { pend = l0; l0 = 0; } else if (l1) { pend = l1; l1 = 0; }
+                    overflow = ((l0 | l1) != 0) || (ending && pend != 0);
                 }
-                lc = c1; lref = m1;                        // a second leaf can only be child 1
-                --n_leaf;
+            } else {
+                // leaf children: one shared test block walked up to twice, so lanes with a single leaf child (either side)
+                // run it together instead of the warp stepping through a copy per side
+                const bool leaf0 = go0 && c0 < 0, leaf1 = go1 && c1 < 0;
+                int lc = leaf0 ? c0 : c1, lref = leaf0 ? m0 : m1;
+                int n_leaf = (leaf0 ? 1 : 0) + (leaf1 ? 1 : 0);
+#pragma unroll 1
+                while (n_leaf > 0) {
+                    const int slot = ~lc;
+                    const float4 *tp = reinterpret_cast<const float4 *>(sc.tri + slot);
+                    float4 q0, q1, q2, q3;
+                    ld256(tp, q0, q1);
+                    if (TRACK) ld256(tp + 2, q2, q3); else q2 = __ldg(tp + 2);
+                    const float eps = TRACK ? q3.x : 0.f;
+                    if (COUNT) nt++;
+                    float t, dt = 0.f; bool edge = false;
+                    const bool hit = tri_test32<TRACK>(q0, q1, q2, eps, o, d, dt_scale, t, edge, dt);
+                    const int ref = lref;                      // leaf: the min-ref field is the triangle itself
+                    const float a = fabsf(t);
+                    const bool ok = hit && (PHYS ? (t > PTB_TMIN_F) : (t * t > PTB_ZERO_F));
+                    if (ok && (a < h.abs_t || (a == h.abs_t && ref < best_ref))) {
+                        if (TRACK) {
+                            if (h.slot >= 0) uc.comp_lo = fminf(uc.comp_lo, h.abs_t - uc.best_dt);
+                            uc.best_dt = dt; uc.best_edge = edge;
+                        }
+                        h.t = t; h.abs_t = a; h.slot = slot; best_ref = ref;
+                    } else if (TRACK && (hit || edge)) {
+                        uc.comp_lo = fminf(uc.comp_lo, a - dt);
+                    }
+                    lc = c1; lref = m1;                        // a second leaf can only be child 1
+                    --n_leaf;
+                }
             }
             go0 = go0 && c0 >= 0; go1 = go1 && c1 >= 0;
 #if PTB_FLAT_STEP_CLOSEST

@@ -123,6 +123,35 @@ def replicate_renderer(scene, device, src=0, group=None, accel=0, make=None):
     return r if rank == src else make(scene, device, accel, blob)
 
 
+def gather_scene_arrays(scene, device, rank=None, world=None, group=None):
+    """The big scene arrays (FP64 vertices and normals, object ids: 100 B per triangle, 1.0 GB at 10^7 triangles) on
+    every rank's GPU with each byte crossing PCIe ONCE: rank g uploads rows [g n / G, (g + 1) n / G) from its
+    (page-locked) host copy and one all-gather over NVLink completes the arrays everywhere.  Returns the tuple
+    `Renderer(scene, device_arrays=...)` takes.  Every rank still holds the host scene (the small tables - materials,
+    light areas - are read from it); what is saved is (G - 1) / G of the host-to-device traffic per rank."""
+    import torch
+    import torch.distributed as dist
+    if world is None:
+        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        rank = dist.get_rank(group) if world > 1 else 0
+    flat = scene.flatten() if hasattr(scene, "flatten") else scene
+    n = int(np.asarray(flat["verts"]).shape[0])
+    per = (n + world - 1) // world
+    lo, hi = min(n, rank * per), min(n, (rank + 1) * per)
+    out = []
+    for key, dt, width in (("verts", torch.float64, 9), ("normals", torch.float64, 3), ("tri_obj", torch.int32, 1)):
+        host = torch.from_numpy(np.asarray(flat[key]).reshape(n, width))
+        mine = torch.zeros((per, width), dtype=dt, device=device)
+        mine[:hi - lo].copy_(host[lo:hi], non_blocking=True)       # this rank's rows, the only ones it reads from the host
+        if world > 1:
+            full = torch.empty((per * world, width), dtype=dt, device=device)
+            dist.all_gather_into_tensor(full, mine, group=group)
+        else:
+            full = mine
+        out.append(full[:n].contiguous() if full.shape[0] != n else full)
+    return out[0].view(n, 3, 3), out[1], out[2].view(n)
+
+
 def render_step(renderer, spp, bounces, seed, width, height, rank=0, world=1, mode="tile", tile=None, full=None,
                 flags=0, tonemap=True):
     """One frame on this rank's share of the work; returns the u8 image tensor on rank 0 (else None)
@@ -184,6 +213,14 @@ def multi_gpu_check(renderer, rank, world, width=256, height=256, spp=8, bounces
         same = torch.tensor([1 if torch.equal(a_rep, a_own) else 0], dtype=torch.int32, device=renderer.device)
         if world > 1:
             dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        arr = Renderer(lbvh_scene, device=renderer.device.index, accel=2,
+                       device_arrays=gather_scene_arrays(lbvh_scene, renderer.device, rank, world))
+        a_arr, _ = arr.trace_paths(2, 3, seed=4, width=96, height=96)
+        same_arr = torch.tensor([1 if torch.equal(a_arr, a_own) else 0], dtype=torch.int32, device=renderer.device)
+        if world > 1:
+            dist.all_reduce(same_arr, op=dist.ReduceOp.MIN)
+        out["gathered_arrays_bitwise"] = bool(same_arr.item())
+        arr.close()
         out["replica_bitwise"] = bool(same.item())
         out["replica_built_on_rank0_only"] = bool(rank == 0 or rep.info()["build_ms"] == 0.0)
         rep.close(); own.close()

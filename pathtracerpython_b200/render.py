@@ -49,10 +49,13 @@ def _dev_key(device):
 
 
 class Renderer:
-    def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None, bvh=None):
+    def __init__(self, scene, device=None, accel=_lib.ACCEL_AUTO, workspace_bytes=None, bvh=None, device_arrays=None):
         """`bvh`: a uint8 device tensor from another Renderer's `export_bvh()` of the SAME scene (possibly
         received from another rank, dist.replicate_renderer): the hierarchies are copied from it
-        (ptb_bvh_import) instead of being built."""
+        (ptb_bvh_import) instead of being built.
+        `device_arrays`: (verts float64 [n,3,3], normals float64 [n,3], tri_obj int32 [n]) torch tensors already on the
+        renderer's device (PTB_SCENE_ARRAYS_ON_DEVICE; dist.gather_scene_arrays assembles them from per-rank slices
+        over NVLink): the big arrays are then not read from the host at all.  LBVH scenes only."""
         torch = _torch()
         self.torch = torch
         self.scene = Scene(scene) if isinstance(scene, str) else scene
@@ -72,6 +75,13 @@ class Renderer:
         d.n_obj = self._keep[3].shape[0]
         d.n_light_tri = d.n_tri - d.n_tri_obj
         d.verts, d.normals, d.tri_obj, d.mat, d.light_areas = [a.ctypes.data for a in self._keep]
+        if device_arrays is not None:
+            dv, dn, do = device_arrays
+            if (dv.dtype != torch.float64 or dn.dtype != torch.float64 or do.dtype != torch.int32 or dv.numel() != 9 * d.n_tri
+                    or dn.numel() != 3 * d.n_tri or do.numel() != d.n_tri or any(t.device != self.device or not t.is_contiguous() for t in (dv, dn, do))):
+                raise PtbError("device_arrays: contiguous float64 [n,3,3], float64 [n,3], int32 [n] tensors on the renderer's device")
+            d.verts, d.normals, d.tri_obj = dv.data_ptr(), dn.data_ptr(), do.data_ptr()
+            d.reserved = _lib.SCENE_ARRAYS_ON_DEVICE
         d.eye[:] = [float(x) for x in f["eye"]]
         d.ortho[:] = [float(x) for x in f["ortho"]]
         d.ambient = float(f["ambient"])

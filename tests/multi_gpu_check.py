@@ -34,7 +34,7 @@ def main():
         assert res["tile_bitwise"], "tile-sharded frame differs from the single-GPU frame"
         assert res["sample_max_rel"] < 1e-4 or res["sample_max_abs"] < 1e-4, res
         print(f"multi-GPU check ok on {world} ranks: tile sharding bitwise identical, sample sharding within {res['sample_max_abs']:.2e}")
-    assert res["replica_bitwise"] and res["replica_built_on_rank0_only"], res
+    assert res["replica_bitwise"] and res["replica_built_on_rank0_only"] and res["gathered_arrays_bitwise"], res
     small = pdist.replicate_renderer(ptb.CORNELL_SDL, local, src=0)      # nothing to export: every rank builds
     assert small.info()["accel"] == "brute"
     if rank == 0:

@@ -133,3 +133,27 @@ def test_replicate_renderer_protocol_gloo(tmp_path):
     mp.spawn(_replicate_worker, args=(2, _free_port(), -1, out), nprocs=2, join=True)
     r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
     assert r0["error"] == "MemoryError" and r1["error"] == "RuntimeError" and r1["made"] == []
+
+
+def _gather_arrays_worker(rank, world, port, n, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(3)
+    flat = {"verts": rng.normal(size=(n, 3, 3)), "normals": rng.normal(size=(n, 3)), "tri_obj": rng.integers(0, 7, n).astype(np.int32)}
+    v, nr, o = pdist.gather_scene_arrays(flat, "cpu")
+    ok = np.array_equal(v.numpy(), flat["verts"]) and np.array_equal(nr.numpy(), flat["normals"]) and np.array_equal(o.numpy(), flat["tri_obj"])
+    torch.save({"ok": ok, "shapes": (tuple(v.shape), tuple(nr.shape), tuple(o.shape))}, f"{out}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_scene_arrays_assembled_from_per_rank_slices_gloo(tmp_path):
+    """dist.gather_scene_arrays: each rank contributes its rows, one all-gather completes the arrays everywhere; a
+    triangle count that does not divide by the rank count goes through the padded tail."""
+    out = str(tmp_path / "ga")
+    for n in (1001, 64):
+        mp.spawn(_gather_arrays_worker, args=(2, _free_port(), n, out), nprocs=2, join=True)
+        for r in range(2):
+            res = torch.load(f"{out}.{r}")
+            assert res["ok"] and res["shapes"] == ((n, 3, 3), (n, 3), (n,))

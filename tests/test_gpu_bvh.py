@@ -340,6 +340,29 @@ def test_bvh_export_import_is_bitwise_identical(cornell, tess8):
     small.close(); built.close(); imp.close()
 
 
+def test_scene_arrays_already_on_the_device(tess8, cornell):
+    """PTB_SCENE_ARRAYS_ON_DEVICE: the FP64 arrays come as device pointers (dist.gather_scene_arrays assembles them from
+    per-rank slices); the scene that results is the one the host upload gives, bit for bit."""
+    import torch
+    from pathtracerpython_b200 import dist as pdist
+    arrays = pdist.gather_scene_arrays(tess8, torch.device("cuda", 0), 0, 1)
+    a = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH, device_arrays=arrays)
+    b = ptb.Renderer(tess8, device=0, accel=ptb.ACCEL_LBVH)
+    assert torch.equal(a.export_bvh(), b.export_bvh())
+    xa, ra = a.trace_paths(3, 4, seed=6, width=96, height=96, records=True)
+    xb, rb = b.trace_paths(3, 4, seed=6, width=96, height=96, records=True)
+    assert torch.equal(xa, xb)
+    for k in ra:
+        assert torch.equal(ra[k], rb[k]), k
+    ta, _ = a.trace_primary(128, 128, precision=ptb.PREC_FP64)
+    tb, _ = b.trace_primary(128, 128, precision=ptb.PREC_FP64)
+    assert torch.equal(ta, tb)
+    with pytest.raises(ptb.PtbError, match="LBVH"):
+        ptb.Renderer(cornell, device=0, accel=ptb.ACCEL_BRUTE,
+                     device_arrays=pdist.gather_scene_arrays(cornell, torch.device("cuda", 0), 0, 1))
+    a.close(); b.close()
+
+
 def _has_plane_ids(r):
     import struct
     return struct.unpack("<i", r.export_bvh()[20:24].cpu().numpy().tobytes())[0]
