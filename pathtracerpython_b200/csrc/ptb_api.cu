@@ -759,6 +759,23 @@ static int scene_create_impl(const ptb_scene_desc *desc, const void *d_blob, siz
         s->n_nodes = n - 1;
         }
     }
+#if PTB_TOP_K > 0
+    if (accel == PTB_ACCEL_LBVH && n < (1 << 24)) {      // reference indices share a word with the plane ids in a TopNode
+        // breadth-first tops of both trees, staged in shared memory by every block of the traversal kernels
+        TopNode *tops = nullptr; int *d_cnt = nullptr;
+        if (scene_malloc((void **)&tops, 2 * (size_t)PTB_TOP_K * sizeof(TopNode) + 64, st) != cudaSuccess) { ptb_scene_destroy(s); set_error("out of device memory"); return PTB_ERR_CUDA; }
+        s->allocs.push_back(tops);
+        d_cnt = (int *)(tops + 2 * PTB_TOP_K);
+        int h_cnt[2] = {0, 0};
+        k_build_top<<<1, 32, 0, st>>>(d.nodes, PTB_TOP_K, tops, d_cnt);
+        if (d.nodes_occ) k_build_top<<<1, 32, 0, st>>>(d.nodes_occ, PTB_TOP_K, tops + PTB_TOP_K, d_cnt + 1);
+        g_launches += d.nodes_occ ? 2 : 1;
+        cudaMemcpyAsync(h_cnt, d_cnt, sizeof(h_cnt), cudaMemcpyDeviceToHost, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess) { ptb_scene_destroy(s); set_error("top-of-tree build failed: %s", cudaGetErrorString(cudaGetLastError())); return PTB_ERR_CUDA; }
+        d.top = tops; d.top_n = h_cnt[0];
+        d.top_occ = d.nodes_occ ? tops + PTB_TOP_K : nullptr; d.top_occ_n = h_cnt[1];
+    }
+#endif
     pt_.mark("hierarchies");
     PTB_CUDA(cudaStreamSynchronize(st));   // host staging vectors go out of scope
     *out = s;

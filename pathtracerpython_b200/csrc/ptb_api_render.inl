@@ -102,15 +102,15 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (track)
-                k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
+                k_closest_bvh32_dyn<true, false><<<grid, PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else if (origin_pid && q.count_nodes)
-                k_closest_bvh32_dyn<false, true, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
+                k_closest_bvh32_dyn<false, true, false, true><<<grid, PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
             else if (origin_pid)
-                k_closest_bvh32_dyn<false, false, false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
+                k_closest_bvh32_dyn<false, false, false, true><<<grid, PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order, origin_pid);
             else if (q.count_nodes)
-                k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
+                k_closest_bvh32_dyn<false, true><<<grid, PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
             else
-                k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
+                k_closest_bvh32_dyn<false, false><<<grid, PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
         } else if (track)
             k_closest_bvh32<true, false><<<grid, PTB_BVH_THREADS, 0, st>>>(s->d, q.qo[in], q.qd[in], d_count, hit_t, hit_tri, q.unc_count, q.unc_list, s->dt_scale);
         else if (q.count_nodes)
@@ -339,13 +339,13 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
             if (origin_pid && q.count_nodes)
-                k_shadow_bvh32_dyn<true, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
+                k_shadow_bvh32_dyn<true, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
             else if (origin_pid)
-                k_shadow_bvh32_dyn<false, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
+                k_shadow_bvh32_dyn<false, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
             else if (q.count_nodes)
-                k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
+                k_shadow_bvh32_dyn<true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             else
-                k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
+                k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             PTB_LAUNCHED();
             k_nee_finish32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
         } else if (d.accel == PTB_ACCEL_LBVH) {
@@ -392,7 +392,7 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
         if (lbvh) {
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
-            k_closest_bvh32_dyn<false, false, true><<<grid_for(upper, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
+            k_closest_bvh32_dyn<false, false, true><<<grid_for(upper, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(
                 d, q.qo[in], q.qd[in], q.count + b, q.hit_t, q.hit_tri, q.unc_count, q.unc_list, s->dt_scale, work, order);
         } else {
             k_closest_planes32<true><<<grid_for(upper, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem, st>>>(
@@ -424,7 +424,7 @@ static int run_batch_phys32(const ptb_scene *s, const ptb_render_params *p, Queu
         if (lbvh) {
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
-            k_shadow_bvh32_dyn<false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(
+            k_shadow_bvh32_dyn<false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(
                 d, q.sh_p, q.sh_d, q.count_sh + b, q.sh_res, q.cap, work, nullptr);
         } else {
             k_shadow_planes_phys32<<<grid_for(N, PTB_TRACE_THREADS, 8), PTB_TRACE_THREADS, smem, st>>>(

@@ -250,6 +250,49 @@ k_pack(int n, const int *__restrict__ sorted_tri, const Aabb *__restrict__ tri_b
 
 // Scene extent, max |coordinate| and a tri_obj range check in one pass; every block writes 8 doubles
 // (min xyz, max xyz, max abs, bad-object flag) that the host folds.
+// Breadth-first top of a finished hierarchy (TopNode, ptb_scene.cuh): one warp walks the tree level by level, 32 queue
+// entries at a time; an inner child gets the next top slot while slots last, else its link points into the full array.
+__global__ void __launch_bounds__(32)
+k_build_top(const BvhNode *__restrict__ nodes, int k_max, TopNode *__restrict__ top, int *__restrict__ top_count) {
+    __shared__ int q[PTB_TOP_OFF];
+    const int lane = threadIdx.x;
+    if (lane == 0) q[0] = 0;
+    __syncwarp();
+    int head = 0, tail = 1;
+    while (head < tail) {
+        const int batch = min(32, tail - head);
+        const bool on = lane < batch;
+        BvhNode nd;
+        int c0 = -1, c1 = -1;
+        if (on) {
+            nd = nodes[q[head + lane]];
+            c0 = nd.c0;
+            const int i1 = (c0 ^ (c0 >> 31)) + 1;
+            c1 = i1 ^ (nd.meta >> 31);
+        }
+        const int in0 = (on && c0 >= 0) ? 1 : 0, in1 = (on && c1 >= 0) ? 1 : 0;
+        int incl = in0 + in1;
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        const int base = tail + incl - (in0 + in1);
+        if (on) {
+            int l0 = c0, l1 = c1;
+            if (in0) { if (base < k_max) { q[base] = c0; l0 = base; } else l0 = c0 + PTB_TOP_OFF; }
+            if (in1) { const int s1 = base + in0; if (s1 < k_max) { q[s1] = c1; l1 = s1; } else l1 = c1 + PTB_TOP_OFF; }
+            TopNode t;
+            t.a = make_float4(nd.lo0x, nd.lo0y, nd.lo0z, nd.hi0x);
+            t.b = make_float4(nd.hi0y, nd.hi0z, nd.lo1x, nd.lo1y);
+            t.c = make_float4(nd.lo1z, nd.hi1x, nd.hi1y, nd.hi1z);
+            t.d = make_int4(l0, l1, nd.n0 | ((nd.meta & 0xff) << 24), nd.n1 | (((nd.meta >> 8) & 0xff) << 24));
+            top[head + lane] = t;
+        }
+        __syncwarp();
+        tail = min(k_max, tail + total);
+        head += batch;
+    }
+    if (lane == 0) *top_count = tail;
+}
+
 // Scene arrays that are already on the device (PTB_SCENE_ARRAYS_ON_DEVICE): the two small tables the host otherwise
 // derives from its copy - the light's vertices in FP32 (utils.py:41-46 reads them per light sample) and the first
 // triangle of every object (the lowest-occluder rule of the shadow walk) - come from these kernels instead.

@@ -51,6 +51,57 @@ namespace ptb {
 #endif
 #define PTB_WW_DONE ((int)0x80000000)   // traversal state: nothing left (leaf codes are ~slot > INT_MIN)
 
+// ---------------------------------------------------------------- the top of the tree in shared memory (PTB_TOP_K > 0)
+#if PTB_TOP_K > 0
+#define PTB_DYN_SMEM ((size_t)PTB_TOP_K * sizeof(TopNode) + 16)
+// One TMA bulk copy (cp.async.bulk global -> shared, completion on an mbarrier) brings the breadth-first top of a tree
+// into this block's shared memory; every thread of the block waits on the barrier's phase 0 before its first fetch.
+__device__ __forceinline__ const TopNode *stage_top(const TopNode *__restrict__ top, int n_top) {
+    extern __shared__ __align__(128) unsigned char s_top_raw[];
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(s_top_raw);
+    const unsigned mb = dst + (unsigned)(PTB_TOP_K * sizeof(TopNode));
+    const unsigned bytes = (unsigned)n_top * (unsigned)sizeof(TopNode);
+    if (n_top <= 0) return reinterpret_cast<const TopNode *>(s_top_raw);     // no top (>= 2^24 triangles): walks start in the full array
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(top), "r"(bytes), "r"(mb) : "memory");
+    }
+    __syncthreads();                    // the barrier is initialised before anybody polls it
+    unsigned done = 0;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(mb) : "memory");
+    } while (!done);
+    return reinterpret_cast<const TopNode *>(s_top_raw);
+}
+// a node of either range: top nodes (< PTB_TOP_OFF) out of shared memory, the rest with the two 256-bit loads of ld_node,
+// their inner links shifted into the full-array range
+__device__ __forceinline__ NodeBoxes ld_node_top(const BvhNode *__restrict__ nodes, const TopNode *s_top, int node) {
+    NodeBoxes n;
+    if (node < PTB_TOP_OFF) {
+        const TopNode *t = s_top + node;
+        n.a = t->a; n.b = t->b; n.c = t->c;
+        const int4 d = t->d;
+        n.d = make_int4(d.x, d.y, d.z & 0xffffff, d.w & 0xffffff);
+        n.pid0 = (int)((unsigned)d.z >> 24); n.pid1 = (int)((unsigned)d.w >> 24);
+    } else {
+        n = ld_node(nodes, node - PTB_TOP_OFF);
+        if (n.d.x >= 0) n.d.x += PTB_TOP_OFF;
+        if (n.d.y >= 0) n.d.y += PTB_TOP_OFF;
+    }
+    return n;
+}
+#define PTB_LD_NODE(nodes, s_top, node) ld_node_top(nodes, s_top, node)
+#define PTB_ROOT root_node
+#else
+#define PTB_DYN_SMEM ((size_t)0)
+#define PTB_LD_NODE(nodes, s_top, node) ld_node(nodes, node)
+#define PTB_ROOT 0
+#endif
+
 // warp-wide claim of new work items for the lanes with want == true; returns the claimed index or
 // 0xffffffff when the pool [0, count) is exhausted.
 __device__ __forceinline__ unsigned claim_work(bool want, unsigned *work, unsigned count) {
@@ -76,9 +127,13 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                     float *__restrict__ hit_t, int *__restrict__ hit_tri, unsigned *unc_count, int *unc_list, float dt_scale,
                     unsigned *work, const unsigned *__restrict__ order, const int *__restrict__ origin_pid = nullptr) {
     const unsigned count = *d_count;
+#if PTB_TOP_K > 0
+    const TopNode *s_top = stage_top(sc.top, sc.top_n);
+    const int root_node = sc.top_n > 0 ? 0 : PTB_TOP_OFF;
+#endif
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
-    int sp = 0, node = 0, best_ref = 0x7fffffff, opid = -1, pend = 0;
+    int sp = 0, node = PTB_ROOT, best_ref = 0x7fffffff, opid = -1, pend = 0;
     unsigned ray = 0xffffffffu;
     bool exhausted = false;                 // warp-uniform: the pool ran dry
     Hit32 h; h.t = 0.f; h.abs_t = 0.f; h.slot = -1;
@@ -96,14 +151,14 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
                 lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
                 h.t = 0.f; h.abs_t = 3.0e38f; h.slot = -1; best_ref = 0x7fffffff;
                 uc.init();
-                sp = 0; node = 0; pend = 0;
+                sp = 0; node = PTB_ROOT; pend = 0;
                 if (PID) { const int pr = origin_pid[ray]; opid = pr ? pr : -1; }
             }
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
         }
         if (!__any_sync(0xffffffffu, ray != 0xffffffffu)) break;
         while (ray != 0xffffffffu) {
-            const NodeBoxes n = ld_node(sc.nodes, node);
+            const NodeBoxes n = PTB_LD_NODE(sc.nodes, s_top, node);
             if (COUNT) nn++;
             float tn0, tf0, tn1, tf1;
             slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);
@@ -228,6 +283,10 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
     const BvhNode *__restrict__ nodes = sc.nodes_occ ? sc.nodes_occ : sc.nodes;
     const TriRec *__restrict__ tris = sc.nodes_occ ? sc.tri_occ : sc.tri;
     const unsigned paths = *d_count;
+#if PTB_TOP_K > 0
+    const TopNode *s_top = sc.nodes_occ ? stage_top(sc.top_occ, sc.top_occ_n) : stage_top(sc.top, sc.top_n);
+    const int root_node = (sc.nodes_occ ? sc.top_occ_n : sc.top_n) > 0 ? 0 : PTB_TOP_OFF;
+#endif
 #if PTB_SHADOW_GROUP
     // work items in groups of PTB_SHADOW_GROUP paths x 3 samples: the lanes that finish sample s of a group of neighbouring
     // paths claim sample s + 1 of the same paths next, while the nodes those paths walk are still in this SM's L1
@@ -237,7 +296,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
 #endif
     unsigned nn = 0, nt = 0;
     int stack[PTB_BVH_STACK];
-    int sp = 0, node = 0, found = 0x7fffffff, found_obj = -1, opid = -1;
+    int sp = 0, node = PTB_ROOT, found = 0x7fffffff, found_obj = -1, opid = -1;
     unsigned item = 0xffffffffu, out_slot = 0;
     bool exhausted = false, want_min = false;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(1.f, 0.f, 0.f);
@@ -265,7 +324,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
                 lb.set(o.x, o.y, o.z, d.x, d.y, d.z);
                 want_min = !PHYS && s == 2u;
                 found = 0x7fffffff; found_obj = -1;
-                sp = 0; node = 0;
+                sp = 0; node = PTB_ROOT;
                 if (PID) { const int pr = origin_pid[j]; opid = pr ? pr : -1; }
             }
             exhausted = __any_sync(0xffffffffu, want && idx == 0xffffffffu);
@@ -276,7 +335,7 @@ k_shadow_bvh32_dyn(DScene sc, const float4 *__restrict__ sh_p, const float4 *__r
         // so the ~80-instruction test block executes with many lanes instead of one or two per node step.
         while (item != 0xffffffffu) {
             while (node >= 0) {
-                const NodeBoxes n = ld_node(nodes, node);
+                const NodeBoxes n = PTB_LD_NODE(nodes, s_top, node);
                 if (COUNT) nn++;
                 float tn0, tf0, tn1, tf1;
                 slab(lb, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y, tn0, tf0);

@@ -46,7 +46,10 @@ template <bool VOTE, bool CLOSEST>
 __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_occ, int n_planes, const float4 pk, const float4 d0,
                                                 const float4 d1, const float4 d2, const float4 dc, bool live, bool &occ0,
                                                 bool &occ1, int &leak_ref, float &best_t, int &best_ref) {
-    occ0 = !live; occ1 = !live;
+    // "sample s is occluded" is carried in its distance limit: -1 once an occluder is found (and from the start for dead
+    // lanes), so that s < lim is never true again - the same outcomes as shadow_planes32's `!occ && ...` without the
+    // flag registers and their predicate conversions in every iteration
+    float lim0 = live ? d0.w : -1.0f, lim1 = live ? d1.w : -1.0f;
     leak_ref = live ? 0x7fffffff : -1;
     float best_a = live ? 3.0e38f : 0.f;
     best_t = 0.f;
@@ -64,8 +67,8 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
         const float2 sA = mul2(tA, tA);
         const float s2 = tB.x * tB.x;
         // main.py:47-51: 1e-5 <= d2 < light_squared_distance ; utils.py:117: |n.d| > 1e-5
-        const bool ok0 = !occ0 && (fabsf(dnA.x) > PTB_ZERO_F) && (sA.x >= PTB_ZERO_F) && (sA.x < d0.w);
-        const bool ok1 = !occ1 && (fabsf(dnA.y) > PTB_ZERO_F) && (sA.y >= PTB_ZERO_F) && (sA.y < d1.w);
+        const bool ok0 = (fabsf(dnA.x) > PTB_ZERO_F) && (sA.x >= PTB_ZERO_F) && (sA.x < lim0);
+        const bool ok1 = (fabsf(dnA.y) > PTB_ZERO_F) && (sA.y >= PTB_ZERO_F) && (sA.y < lim1);
         const bool ok2 = (planes[g].ref_a < leak_ref) && (fabsf(dnB.x) > PTB_ZERO_F) && (s2 >= PTB_ZERO_F) && (s2 < d2.w);
         const float atc = fabsf(tB.y);
         const bool okc = CLOSEST && (fabsf(dnB.y) > PTB_ZERO_F) && (atc > PTB_TMIN_F) && (atc < best_a);
@@ -77,8 +80,8 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
             float2 uA, uB; bool h0, h1, h2, hc;
             para2(a1, a2, pxA, pyA, pzA, uA, h0, h1);
             para2(a1, a2, pxB, pyB, pzB, uB, h2, hc);
-            occ0 = occ0 || (ok0 && h0);
-            occ1 = occ1 || (ok1 && h1);
+            if (ok0 && h0) lim0 = -1.0f;
+            if (ok1 && h1) lim1 = -1.0f;
             if (ok2 && h2) leak_ref = min(leak_ref, uB.x > 0.0f ? planes[g].ref_a : planes[g].ref_b);
             if (CLOSEST && hc && okc) { best_a = atc; best_t = tB.y; best_ref = uB.y > 0.0f ? planes[g].ref_a : planes[g].ref_b; }
         } else {
@@ -95,8 +98,8 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
                 hb2 = bary_min(b1, b2, pxB.x, pyB.x, pzB.x) > 0.0f;
                 if (CLOSEST) mbc = bary_min(b1, b2, pxB.y, pyB.y, pzB.y);
             }
-            occ0 = occ0 || (ok0 && (ha0 || hb0));
-            occ1 = occ1 || (ok1 && (ha1 || hb1));
+            if (ok0 && (ha0 || hb0)) lim0 = -1.0f;
+            if (ok1 && (ha1 || hb1)) lim1 = -1.0f;
             if (ok2 && (ha2 || hb2)) leak_ref = min(leak_ref, ha2 ? planes[g].ref_a : planes[g].ref_b);
             if (CLOSEST) {
                 // A precedes B in reference order; both lie in the same plane (same |t|), so A wins a tie
@@ -105,6 +108,7 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
             }
         }
     }
+    occ0 = lim0 < 0.0f; occ1 = lim1 < 0.0f;
     if (CLOSEST) {
         // the light's planes: not occluders (main.py:42), the new ray alone (closest_planes32's loop body)
         for (int g = n_occ; g < n_planes; ++g) {

@@ -28,6 +28,18 @@ struct BvhNode {
 };
 #define PTB_PLANE_IDS 255        // plane ids 1..255; 0 = none / mixed
 
+// The TOP of a hierarchy - its first PTB_TOP_K inner nodes in breadth-first order - as a tile every block of the
+// traversal kernels stages in SHARED memory (one TMA bulk copy at block start, ptb_bvh_dyn.cuh): a 64 B gather out of
+// shared memory runs at 340-470 Gfetch/s against 200 out of L1 (ptb_gather_peak_smem / ptb_gather_peak), and every walk
+// starts with these nodes.  64 B like BvhNode but with BOTH child links explicit (breadth-first numbering breaks the
+// "child 1 = position of child 0 + 1" rule): d = (c0, c1, n0 | pid0 << 24, n1 | pid1 << 24).  A link < 0 is a leaf
+// (~slot), 0 <= link < PTB_TOP_OFF another top node, link >= PTB_TOP_OFF the node link - PTB_TOP_OFF of the full array.
+struct TopNode { float4 a, b, c; int4 d; };
+#ifndef PTB_TOP_K
+#define PTB_TOP_K 0              // nodes staged per block (0: off); 256 = 16 KB
+#endif
+#define PTB_TOP_OFF 4096         // first index of the "full array" range in a walk's node variable
+
 struct DScene {
     // --- FP32 product path
     const TriRec *tri;        // [n_tri] in reference order (brute force) or BVH leaf order
@@ -53,6 +65,8 @@ struct DScene {
     const TriRec *tri_occ;    // leaf-ordered records of the occlusion set
     const int *tri_id_occ;
     const unsigned char *tri_pid; // [n_tri] by reference index: supporting-plane id of the triangle (0: none); null when unused
+    const TopNode *top, *top_occ; // [top_n], [top_occ_n] breadth-first top of either tree (null: not built)
+    int top_n, top_occ_n;
     int n_tri, n_tri_obj, n_obj, n_light_tri;
     int accel;
     double eye[3], ortho[4], ambient, light_color[3];

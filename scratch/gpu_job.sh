@@ -13,17 +13,18 @@ except Exception as e:
 PY
 }
 echo "== Cornell headline: blocks per SM of the packed kernel (base = 4, 64 registers)"
-for v in base mb3 mb5; do
+for v in base mb3 mb5 lim; do
   PTB_LIB_PATH=$PWD/scratch/ab/libptb_$v.so python bench.py --steps 4 --warmup 3 --no-secondary --no-cpu-baseline > gpurun_out/bench_cornell_$v.json 2> gpurun_out/bench_cornell_$v.err
   summ gpurun_out/bench_cornell_$v.json
 done
 echo "== LBVH 1 M triangles, 64 spp: base vs pending-leaf slot in the closest-hit kernel"
-for v in base defer; do
+for v in base defer top64 top256 top256defer; do
   PTB_LIB_PATH=$PWD/scratch/ab/libptb_$v.so python bench.py --tess 177 --spp 64 --steps 3 --warmup 3 --no-secondary --no-cpu-baseline > gpurun_out/bench_c4_$v.json 2> gpurun_out/bench_c4_$v.err
   summ gpurun_out/bench_c4_$v.json
 done
-echo "== LBVH tests with the pending-leaf build"
+echo "== LBVH tests with the pending-leaf build, then with the staged top + pending leaf"
 PTB_LIB_PATH=$PWD/scratch/ab/libptb_defer.so python -m pytest tests/test_gpu_bvh.py -m gpu -q -k "not million and not file_loader" 2>&1 | tail -5
+PTB_LIB_PATH=$PWD/scratch/ab/libptb_top256defer.so python -m pytest tests/test_gpu_bvh.py tests/test_gpu_physical.py tests/test_gpu_soup.py -m gpu -q -k "not ten_million and not file_loader" 2>&1 | tail -8
 echo "== ncu: Cornell 64 spp launch list + full capture of the packed fused kernel"
 CMD="python bench.py --spp 64 --steps 1 --warmup 3 --no-secondary --no-cpu-baseline"
 $CMD > gpurun_out/r02c_plain_cornell_spp64.json 2> gpurun_out/r02c_plain_cornell_spp64.err &&
