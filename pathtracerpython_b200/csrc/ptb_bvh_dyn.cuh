@@ -47,7 +47,7 @@ namespace ptb {
 // with one or two lanes (a lane meets a leaf in 7 % of its node steps, a 16-lane warp in 69 % of them).  Costs: the hit is
 // known a few steps later, so the pruning bound shrinks later and a ray visits a few more nodes (counted: PTB_FLAG_COUNT_NODES).
 #ifndef PTB_CLOSEST_DEFER
-#define PTB_CLOSEST_DEFER 0
+#define PTB_CLOSEST_DEFER 1
 #endif
 #define PTB_WW_DONE ((int)0x80000000)   // traversal state: nothing left (leaf codes are ~slot > INT_MIN)
 
