@@ -54,6 +54,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="headline workload only")
     ap.add_argument("--secondary-steps", type=int, default=2)
+    ap.add_argument("--no-e2e-variants", action="store_true", help="N > 1, LBVH scenes: time only the per-rank-upload end-to-end step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the bounded baseline sample")
     ap.add_argument("--config1", action="store_true", help="BASELINE.json configs[0]: the shipped 40x40 scene at -r 10 -b 2, "
                     "GPU next to the UNMODIFIED Python reference (oracle/_ref) on this host")
@@ -454,6 +455,7 @@ def roofline(ctx, spec, r, prof, ctr, info):
                 "hbm": {"achieved": tk.get("dram_gbs"), "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": tk.get("dram_frac_of_hbm_peak"),
                         "peak_source": pk["hbm_source"], "note": "MEASURED DRAM traffic, not algorithmic bytes: the trees are served from L1/L2"},
                 "per_ray": {"nodes_closest": n_ch, "tris_closest": t_ch, "nodes_shadow": n_sh, "tris_shadow": t_sh},
+                "executed": (tj or {}).get("lbvh_executed"),
                 "kernels": per_kernel, "launches": launches, "avg_launch_ms": prof[top][0] / max(1, launches), "kernel_ms": kernel_ms,
                 "note": "bound is 'gather', outside the contract's {hbm, tensor}: these kernels fetch 64 B nodes / records that live "
                         "in L1 / L2, DRAM sees a few per cent of the fetched bytes (hbm.frac); frac = fetch rate / L1-resident gather peak"}
@@ -514,7 +516,7 @@ def run_ours(a):
         r0 = ptb.Renderer(ptb.CORNELL_SDL, device=ctx.local)
         mgc = pdist.multi_gpu_check(r0, rank, world, lbvh_scene=synth.tessellate(ptb.Scene(ptb.CORNELL_SDL), 8))
         r0.close()
-    entry, r, _ = measure(ctx, main_spec, a.steps, a.warmup, e2e_replicated=bool(a.tess))
+    entry, r, _ = measure(ctx, main_spec, a.steps, a.warmup, e2e_replicated=bool(a.tess) and not a.no_e2e_variants)
     secondary = []
     if not a.no_secondary and not (a.tess or a.warp or a.scene) and (a.width, a.height, a.spp) == (1024, 1024, 1024):
         ks, kw = max(1, min(a.secondary_steps, a.steps)), 3
@@ -565,7 +567,7 @@ def run_ours(a):
                     line["divergent_ppm"] = par["divergent_ppm"]
                 except Exception as ex:      # noqa: BLE001
                     line["cpu_baseline"]["parity"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:200]}
-                line["cpu_baseline"]["reference_python"] = python_reference_sample(1, 2)
+                line["cpu_baseline"]["reference_python"] = python_reference_sample(4, 2)
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -147,7 +147,7 @@ int ptb_scene_destroy(ptb_scene *scene);
 /* ptb_scene_destroy waits for the streams the handle was used on (not for the device) and frees in stream order.
  * Scene memory is taken from a stream-ordered pool PRIVATE to the library (one per device; the device's default pool is
  * left alone) and returns to it on ptb_scene_destroy, so that creating a scene per frame does not pay the driver's
- * allocator each time.  The pool keeps at most 8 GiB of unused memory across synchronisations; ptb_pool_trim hands
+ * allocator each time.  The pool keeps at most 16 GiB of unused memory across synchronisations; ptb_pool_trim hands
  * all of it back to the driver (synchronises the device). */
 int ptb_pool_trim(void);
 int ptb_scene_info(const ptb_scene *scene, int32_t *accel, int32_t *n_nodes, double *build_ms);

@@ -38,8 +38,8 @@ DeviceState *device_state() {
             // bench.py's end-to-end step) recycles pool memory instead of going to the driver's allocator (cudaFree
             // synchronises the device and was measured at 4-240 ms per scene), and the device's default pool - which other
             // cudaMallocAsync users of the process share - keeps its own release threshold.  The pool holds on to at most
-            // PTB_POOL_KEEP_BYTES of unused memory across synchronisations (a 10 M-triangle scene with its build arena is
-            // 5 GB); ptb_pool_trim hands everything back.
+            // PTB_POOL_KEEP_BYTES of unused memory across synchronisations (two 10 M-triangle scenes with a build arena are
+            // 9 GB); ptb_pool_trim hands everything back.
             ds->pool = nullptr;
             cudaMemPoolProps props;
             memset(&props, 0, sizeof(props));
@@ -54,6 +54,18 @@ DeviceState *device_state() {
                 ds->pool = pool;
             } else {
                 cudaGetLastError();
+            }
+            // PTB_L2_PERSIST_MB=n: set n MB of L2 aside for persisting lines; the LBVH kernels then pin their node array there
+            // (l2_window, ptb_api_render.inl).  Off by default: measured, see DESIGN.md section 4.
+            ds->l2_persist_bytes = 0; ds->l2_window_max = 0;
+            if (const char *mb = getenv("PTB_L2_PERSIST_MB")) {
+                cudaDeviceProp prop;
+                if (atoi(mb) > 0 && cudaGetDeviceProperties(&prop, dev) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+                    const size_t want = std::min<size_t>((size_t)atoi(mb) << 20, (size_t)prop.persistingL2CacheMaxSize);
+                    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+                        ds->l2_persist_bytes = want; ds->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+                    } else cudaGetLastError();
+                }
             }
             ds->ready.store(true, std::memory_order_release);
         }

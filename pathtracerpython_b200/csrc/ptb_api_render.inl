@@ -91,6 +91,22 @@ static size_t smem_tris(int n) { return (size_t)n * sizeof(TriRec); }
 // q.work_slot rotates through the 32 work counters of a queue set; q.count_nodes: instrumented (untimed) run that counts
 // nodes visited / triangles tested.  Both live in the per-call queue set: calls on other streams / threads have their own.
 
+// L2 persistence window over a node array for the launches that follow on `st` (PTB_L2_PERSIST_MB > 0): node fetches that
+// miss L1 then hit L2 instead of going to HBM whatever the ray state streaming through does to the rest of the cache.
+static void l2_window(cudaStream_t st, const void *base, size_t bytes) {
+    DeviceState *ds = device_state();
+    if (!ds->l2_persist_bytes) return;
+    cudaStreamAttrValue v;
+    memset(&v, 0, sizeof(v));
+    const size_t win = std::min(bytes, ds->l2_window_max);
+    v.accessPolicyWindow.base_ptr = const_cast<void *>(base);
+    v.accessPolicyWindow.num_bytes = base ? win : 0;
+    v.accessPolicyWindow.hitRatio = (base && win) ? (float)std::min(1.0, (double)ds->l2_persist_bytes / (double)win) : 0.f;
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
+}
+
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
                             bool track, float *hit_t, int *hit_tri, cudaStream_t st, const unsigned *order = nullptr,
@@ -98,6 +114,7 @@ static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const 
     ProfScope ps_(PK_CLOSEST, st);
     if (s->d.accel == PTB_ACCEL_LBVH) {
         const int grid = grid_for(upper, PTB_BVH_THREADS, 12);
+        l2_window(st, s->d.nodes, sizeof(BvhNode) * (size_t)s->d.n_tri);
         if (s->bvh_dynamic && q.work) {
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
@@ -338,6 +355,7 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
         if (d.accel == PTB_ACCEL_LBVH && s->bvh_dynamic) {
             unsigned *work = q.work + (q.work_slot++ & 31);
             PTB_CUDA(cudaMemsetAsync(work, 0, sizeof(unsigned), st));
+            l2_window(st, d.nodes_occ ? d.nodes_occ : d.nodes, sizeof(BvhNode) * (size_t)(d.nodes_occ ? d.n_tri_obj : d.n_tri));
             if (origin_pid && q.count_nodes)
                 k_shadow_bvh32_dyn<true, false, true><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order, origin_pid);
             else if (origin_pid)

@@ -20,13 +20,15 @@ extern std::atomic<unsigned long long> g_launches;   // kernels launched by this
 // Per-device state of the library.  include/ptb.h lets any host thread call in on any device and stream, so nothing that
 // CUDA keeps per device (kernel attributes, the SM count, the scene memory pool) may hide behind a process-wide flag.
 #define PTB_MAX_DEVICES 64
-#define PTB_POOL_KEEP_BYTES (8ull << 30)   // unused scene memory the private pool keeps across synchronisations
+#define PTB_POOL_KEEP_BYTES (16ull << 30)   // unused scene memory the private pool keeps across synchronisations
 struct DeviceState {
     std::atomic<bool> ready;        // sms / pool filled in
     int sms;                        // multiprocessor count (persistent grids are multiples of it)
     std::atomic<bool> sort_optin;   // k_ps_scatter: 64 KB of dynamic shared memory asked for on this device
     std::atomic<bool> planes_optin; // plane-list kernels: more than 48 KB asked for on this device
     cudaMemPool_t pool;             // private stream-ordered pool of the scene memory (null: creation failed, plain cudaMallocAsync)
+    size_t l2_persist_bytes;        // L2 set aside for persisting lines (PTB_L2_PERSIST_MB; 0: the feature is off)
+    size_t l2_window_max;           // largest access-policy window the device takes
 };
 DeviceState *device_state();        // of the CURRENT device (ptb_api.cu)
 extern std::mutex g_state_mu;       // guards first-use initialisation of a DeviceState and the profiler's lists
