@@ -181,6 +181,22 @@ int ptb_trace_primary(const ptb_scene *scene, const ptb_pixels *px, int32_t prec
 int ptb_trace_closest(const ptb_scene *scene, const void *d_rays, int64_t n, int32_t precision,
                       int32_t *d_tri, void *d_t, void *stream);
 
+/* ptb_trace_closest for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments, same results as ptb_trace_closest (bit for bit); the two ray queues and the count word that
+ * ptb_trace_closest takes from cudaMallocAsync live in a file-scope `static __device__` array of the library instead
+ * (2 x 32 B x PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS + 256 B = 8 MiB + 256 B, held by every GPU that loads the library
+ * until the process exits).  The call makes no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library
+ * routine; more than PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS rays in one call is refused with PTB_ERR_NOMEM and a message
+ * (split the call).  Every call on a device shares the one array, which keeps the last call's contents (the call
+ * clears the word that must start at zero): calls that overlap on the GPU - two streams, two host threads - RACE;
+ * keep them on one stream or order them with events.  LBVH scenes are walked by the static-assignment kernel (the
+ * dynamic-fetch kernel needs a work counter from a workspace). */
+#define PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS 131072
+int ptb_trace_closest_noalloc(const ptb_scene *scene, const void *d_rays, int64_t n, int32_t precision,
+                              int32_t *d_tri, void *d_t, void *stream);
+int64_t ptb_trace_closest_noalloc_max_rays(void);
+
 /* replaces the sample loop x bounce loop of main() (main.py:186-271): for every pixel of the set and
  * every sample in [s0, s1) it ADDS the sample's radiance to d_accum[pixel_slot] (float4: r, g, b,
  * sample count).  The mean (main.py:274-280) is taken by ptb_tonemap / the caller. */

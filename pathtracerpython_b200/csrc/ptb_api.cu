@@ -850,3 +850,73 @@ extern "C" int64_t ptb_pixel_count(const ptb_pixels *px) { return px ? pixel_cou
 
 #include "ptb_api_render.inl"
 #include "ptb_obj.inl"
+
+// ---------------------------------------------------------------- ptb_trace_closest without any allocation
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  ptb_trace_closest takes its two ray queues and the count word from cudaMallocAsync; this variant takes them
+// from a file-scope device array of a fixed, stated size.  Every GPU that loads the library holds the array until
+// exit.  In HOST code the array's name is only a stand-in: the device address is asked for once per device with
+// cudaGetSymbolAddress (that device current) and it is that pointer the kernels get.
+#define PTB_NOALLOC_SCRATCH_BYTES (2 * sizeof(double4) * (size_t)PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS + 256)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PTB_NOALLOC_SCRATCH_BYTES];
+
+namespace ptb {
+static void *g_noalloc_ptr[PTB_MAX_DEVICES];        // device address of g_noalloc_scratch on device i, guarded by g_state_mu
+static int noalloc_scratch(char **out) {
+    int dev = 0;
+    PTB_CUDA(cudaGetDevice(&dev));
+    if ((unsigned)dev >= PTB_MAX_DEVICES) { set_error("device %d: more devices than the library keeps state for", dev); return PTB_ERR_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lk(g_state_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        PTB_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) { set_error("cudaGetSymbolAddress gave no address for the scratch array on device %d", dev); return PTB_ERR_CUDA; }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = (char *)g_noalloc_ptr[dev];
+    return PTB_OK;
+}
+}  // namespace ptb
+
+extern "C" int64_t ptb_trace_closest_noalloc_max_rays(void) { return PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS; }
+
+extern "C" int ptb_trace_closest_noalloc(const ptb_scene *s, const void *d_rays, int64_t n, int32_t precision,
+                                         int32_t *d_tri, void *d_t, void *stream) {
+    int rc;
+    if ((rc = check_scene(s, stream))) return rc;
+    if (!d_rays || !d_tri || !d_t || n < 0) { set_error("ptb_trace_closest_noalloc: bad argument"); return PTB_ERR_ARG; }
+    if (precision != PTB_PREC_FP32 && precision != PTB_PREC_FP64) { set_error("unknown precision %d", precision); return PTB_ERR_ARG; }
+    if (n > PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS) {
+        set_error("ptb_trace_closest_noalloc: %lld rays, the fixed scratch array holds at most %d per call (split the call, or use ptb_trace_closest)",
+                  (long long)n, PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS);
+        return PTB_ERR_NOMEM;
+    }
+    if (n == 0) return PTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    char *scratch = nullptr;
+    if ((rc = noalloc_scratch(&scratch))) return rc;
+    // The array keeps the last call's contents.  Both queues are rewritten for [0, n) before they are read and nothing
+    // beyond n is read; the count word is the one thing a kernel reads that must be right from the start: cleared here,
+    // then set by k_rays_to_queue*.
+    const size_t v = precision == PTB_PREC_FP64 ? sizeof(double4) : sizeof(float4);
+    unsigned *cnt = (unsigned *)(scratch + 2 * v * (size_t)n);
+    PTB_CUDA(cudaMemsetAsync(cnt, 0, 256, st));
+    if (precision == PTB_PREC_FP32) {
+        float4 *qo = (float4 *)scratch, *qd = qo + n;
+        { ProfScope ps_(PK_OTHER, st);
+        k_rays_to_queue32<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const float *)d_rays, n, qo, qd, cnt);
+        }
+        PTB_LAUNCHED();
+        Queues<float> q; memset(&q, 0, sizeof(q));
+        q.qo[0] = qo; q.qd[0] = qd;
+        if ((rc = launch_closest32(s, q, 0, cnt, (size_t)n, false, (float *)d_t, d_tri, st))) return rc;
+    } else {
+        double4 *qo = (double4 *)scratch, *qd = qo + n;
+        { ProfScope ps_(PK_OTHER, st);
+        k_rays_to_queue64<<<grid_for((size_t)n, 256, 8), 256, 0, st>>>((const double *)d_rays, n, qo, qd, cnt);
+        }
+        PTB_LAUNCHED();
+        if ((rc = launch_closest64(s, qo, qd, cnt, (size_t)n, (double *)d_t, d_tri, st))) return rc;
+    }
+    return PTB_OK;
+}

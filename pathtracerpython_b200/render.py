@@ -183,6 +183,16 @@ class Renderer:
                                                     self._stream()), "ptb_trace_closest")
         return tri, t
 
+    def trace_closest_noalloc(self, rays, tri, t, precision=_lib.PREC_FP32):
+        """ptb_trace_closest_noalloc: the same query into caller-owned DEVICE tensors (`rays` [n, 6] float32 / float64
+        contiguous, `tri` int32 [n], `t` like rays [n]); the library allocates nothing (its scratch is a fixed device
+        array), at most `ptb_trace_closest_noalloc_max_rays()` rays per call, calls must not overlap on the GPU."""
+        n = rays.shape[0]
+        with self.torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ptb_trace_closest_noalloc(self._handle, rays.data_ptr(), n, precision, tri.data_ptr(),
+                                                            t.data_ptr(), self._stream()), "ptb_trace_closest_noalloc")
+        return tri, t
+
     # ---- parity seam 2 / the hot path
     def trace_paths(self, n_rays, n_bounces, seed=0, width=None, height=None, shard=0, n_shards=1, tile=4096,
                     pixel_list=None, sample_begin=0, precision=_lib.PREC_FP32, flags=0, records=False, accum=None,
