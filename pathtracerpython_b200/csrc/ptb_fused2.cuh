@@ -135,6 +135,27 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
     }
 }
 
+// Stall samples of the kernel (ncu source page, profiles/r02j_ncu_source_fused_x2.csv) put half of its time OUTSIDE the
+// plane loop that holds two thirds of its instructions; the largest single item was the block-wide compaction - three
+// barriers per tile, every warp of the block waiting out the slot counter's atomic (6 % of the samples).
+// PTB_X2_WARP_COMPACT: slots are claimed per WARP - ballot, one atomic by the leader, shuffle - with no barrier: +3.2 %
+// (2 930 -> 3 022 Msamples/s, profiles/r02k_ab_compact_prefetch.log).  The queue order then depends on the arrival of the
+// warps; nothing downstream depends on it (a path's radiance lives in L[path id], records are indexed by path id), so
+// radiance and records stay bit-identical and deterministic.  Measured with it and dropped: prefetching L[id] and the
+// next tile's queue entries into L2 or L1 ahead of the plane loop (the two loads with the most long-scoreboard samples):
+// -0.3 % / -0.2 .. -1.5 % (profiles/r02k_ab_prefetch_l1.log) - other warps were already covering those waits.
+#ifndef PTB_X2_WARP_COMPACT
+#define PTB_X2_WARP_COMPACT 1
+#endif
+__device__ __forceinline__ unsigned compact_slot_warp(bool alive, unsigned *d_out_count) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned ballot = __ballot_sync(0xffffffffu, alive);
+    unsigned base = 0;
+    if (lane == 0 && ballot) base = atomicAdd(d_out_count, (unsigned)__popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    return base + __popc(ballot & ((1u << lane) - 1u));
+}
+
 #ifndef PTB_FUSED2_MIN_BLOCKS
 #define PTB_FUSED2_MIN_BLOCKS 4
 #endif
@@ -259,7 +280,11 @@ k_bounce_planes32x2(DScene sc, PlaneScene ps, BatchInfo bi, const float4 *__rest
             }
         }
         if (CLOSEST) {
+#if PTB_X2_WARP_COMPACT
+            const unsigned j = compact_slot_warp(alive, d_count_out);
+#else
             const unsigned j = compact_slot(alive, d_count_out);
+#endif
             if (alive) {
                 qo_out[j] = o_new; qd_out[j] = d_new;
                 hit_t_out[j] = t_new; hit_tri_out[j] = tri_new;
