@@ -256,7 +256,9 @@ k_closest_bvh32_dyn(DScene sc, const float4 *__restrict__ qo, const float4 *__re
             } else {                                            // ray finished
 #endif
                 hit_t[ray] = h.t;
-                hit_tri[ray] = h.slot >= 0 ? best_ref : -1;
+                // without TRACK nothing else reads h.slot: 'a hit was found' is best_ref != INT_MAX, and the register h.slot would
+                // occupy is one the kernel does not have (closest-hit kernel -4 %, profiles/r02n_ab_tos_prefetch.log, `base`)
+                hit_tri[ray] = (TRACK ? h.slot >= 0 : best_ref != 0x7fffffff) ? best_ref : -1;
                 if (TRACK && closest_uncertain32<TRACK>(h, uc)) unc_list[atomicAdd(unc_count, 1u)] = (int)ray;
                 ray = 0xffffffffu;
             }

@@ -1,7 +1,6 @@
 #!/bin/bash
-# A/B of library variants scratch/libptb_<name>.so on the 1M-triangle scene: name, Msamples/s, per-kernel ms
-run() { python bench.py --tess ${TESS:-177} --spp ${SPP:-32} --no-cpu-baseline 2>/dev/null | python -c "
+# A/B of library variants scratch/libptb_<name>.so ("cur" = the in-tree library) on a tessellated scene: name, Msamples/s, per-kernel ms
+run() { python bench.py --tess ${TESS:-177} --spp ${SPP:-64} ${EXTRA} --steps 3 --warmup 3 --no-secondary --no-cpu-baseline 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); k=d['roofline']['kernel_ms']; print('$1', round(d['value'],1), {x:k.get(x) for x in ('closest_hit','shadow','shade','ray_sort')})"; }
-run base
-for v in "$@"; do PTB_LIB_PATH=scratch/libptb_$v.so run $v; done
+d=json.loads([l for l in sys.stdin.read().strip().splitlines() if l.startswith('{')][-1]); k=d['roofline']['kernel_ms']; print('$1', round(d['value'],1), {x:k.get(x) for x in ('closest_hit','shadow','shade','ray_sort')})"; }
+for v in "$@"; do if [ "$v" = cur ]; then run cur; else PTB_LIB_PATH=scratch/libptb_$v.so run $v; fi; done
