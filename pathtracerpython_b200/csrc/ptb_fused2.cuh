@@ -147,14 +147,6 @@ __device__ __forceinline__ void trace4_planes32(const PlaneRec *planes, int n_oc
 #ifndef PTB_X2_WARP_COMPACT
 #define PTB_X2_WARP_COMPACT 1
 #endif
-__device__ __forceinline__ unsigned compact_slot_warp(bool alive, unsigned *d_out_count) {
-    const unsigned lane = threadIdx.x & 31;
-    const unsigned ballot = __ballot_sync(0xffffffffu, alive);
-    unsigned base = 0;
-    if (lane == 0 && ballot) base = atomicAdd(d_out_count, (unsigned)__popc(ballot));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    return base + __popc(ballot & ((1u << lane) - 1u));
-}
 
 #ifndef PTB_FUSED2_MIN_BLOCKS
 #define PTB_FUSED2_MIN_BLOCKS 4

@@ -33,7 +33,7 @@ __device__ __forceinline__ unsigned ps_expand10(unsigned v) {  // 10 bits -> eve
     return v;
 }
 __device__ __forceinline__ unsigned ps_key(float x, float y, float z, const float *lo, const float *inv) {
-    const float s = (float)(1 << (PS_KEY_BITS - 8)), top = (float)((1 << PS_KEY_BITS) - 1);
+    const float s = (float)(1 << PS_KEY_BITS) / 256.0f, top = (float)((1 << PS_KEY_BITS) - 1);
     const unsigned ix = (unsigned)fminf(fmaxf((x - lo[0]) * (inv[0] * s), 0.f), top);
     const unsigned iy = (unsigned)fminf(fmaxf((y - lo[1]) * (inv[1] * s), 0.f), top);
     const unsigned iz = (unsigned)fminf(fmaxf((z - lo[2]) * (inv[2] * s), 0.f), top);
