@@ -239,6 +239,10 @@ def test_packed_fp32_kernel_equals_scalar_fused_kernel(monkeypatch):
         packed.close(); scalar.close()
 
 
+def _np(rec):
+    return {k: v.cpu().numpy() for k, v in rec.items()}
+
+
 def test_repeated_frames_are_bitwise_identical(rnd):
     """The fused kernel's survivors claim their queue slots per warp (one atomic per warp, no block-wide scan), so the ORDER
     of the ray queue depends on the arrival of the warps.  Nothing downstream may depend on it: a path's radiance lives in
