@@ -592,8 +592,22 @@ def run_config1(a):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 20
+    # the same frame as a CUDA graph (ProgressiveFrame: ptb_trace_paths_at + tone map captured once, the sample offset advanced
+    # on the device): a 40x40 frame is ~15 launches of microsecond kernels, i.e. launch-bound
+    pf = ptb.ProgressiveFrame(r, 10, 2, seed=a.seed)
+    for _ in range(5):
+        pf.step()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(200):
+        pf.step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_graph = e0.elapsed_time(e1) / 200
     print(json.dumps({"metric": "Msamples/s", "value": 16000 / ms / 1e3, "unit": "Msamples/s", "n_gpus": 1, "ms_per_step": ms,
                       "config": {"workload": "cornell_box_40x40_10spp_b2 (objs/cornellroom.sdl as shipped)"},
+                      "cuda_graph": {"value": 16000 / ms_graph / 1e3, "unit": "Msamples/s", "ms_per_step": ms_graph,
+                                     "note": "the frame's launch sequence replayed as one CUDA graph, fresh samples every replay"},
                       "cpu_baseline": ref, "dtype": "f32"}))
 
 

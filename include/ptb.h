@@ -205,6 +205,15 @@ int ptb_trace_paths(const ptb_scene *scene, const ptb_render_params *p, void *d_
                     size_t workspace_bytes, float *d_accum /* [n_pixel_slots][4] */,
                     const ptb_path_records *records /* may be NULL */, void *stream);
 
+/* ptb_trace_paths with the sample index shifted by a DEVICE word: sample s of the call is sample s + *d_sample_offset of the
+ * stream (main.py:186 `rays_counter`; no counterpart in the reference, whose sample loop lives on the host).  The launch
+ * sequence of a call makes no allocation, no copy from host memory and no synchronisation, so it can be recorded into a CUDA
+ * graph (stream capture); with the offset in device memory - and advanced inside the same graph - every replay adds the
+ * NEXT samples of every pixel to d_accum: progressive rendering of a launch-bound frame (the shipped 40 x 40 scene: fifteen
+ * launches per frame) at the cost of one graph launch.  pathtracerpython_b200.render.ProgressiveFrame is that graph. */
+int ptb_trace_paths_at(const ptb_scene *scene, const ptb_render_params *p, void *d_workspace, size_t workspace_bytes,
+                       float *d_accum, const ptb_path_records *records, const int32_t *d_sample_offset, void *stream);
+
 /* replaces make_image (utils.py:150-161): d_accum is the FULL frame in ray-index order
  * (slot = r); writes the H x W x 3 u8 image, rows top to bottom. d_workspace >= 64 bytes. */
 int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_rgb,

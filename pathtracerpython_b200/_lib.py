@@ -17,7 +17,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
            "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim",
            "ptb_gather_peak", "ptb_gather_peak_smem", "ptb_kat", "ptb_scene_plane_culling",
-           "ptb_trace_closest_noalloc", "ptb_trace_closest_noalloc_max_rays"]
+           "ptb_trace_closest_noalloc", "ptb_trace_closest_noalloc_max_rays", "ptb_trace_paths_at"]
 
 
 class PtbError(RuntimeError):
@@ -85,6 +85,8 @@ def lib():
         L.ptb_trace_paths_workspace.argtypes = [C.POINTER(RenderParams), C.c_int32]
         L.ptb_trace_paths.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
                                       C.POINTER(PathRecords), C.c_void_p]
+        L.ptb_trace_paths_at.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
+                                         C.POINTER(PathRecords), C.c_void_p, C.c_void_p]
         L.ptb_tonemap.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptb_tonemap_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.POINTER(C.c_double),
                                         C.c_void_p, C.c_void_p]

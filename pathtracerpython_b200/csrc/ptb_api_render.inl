@@ -173,7 +173,7 @@ extern "C" int ptb_trace_primary(const ptb_scene *s, const ptb_pixels *px, int32
     if (!d_tri || !d_t || !d_ws) { set_error("ptb_trace_primary: null output/workspace"); return PTB_ERR_ARG; }
     cudaStream_t st = (cudaStream_t)stream;
     BatchInfo bi;
-    bi.pm = make_pixel_map(px); bi.npix = bi.pm.n; bi.S = 1; bi.s_first = 0; bi.bounce = 0; bi.seed = 0;
+    bi.pm = make_pixel_map(px); bi.npix = bi.pm.n; bi.S = 1; bi.s_first = 0; bi.bounce = 0; bi.seed = 0; bi.s_off = nullptr;
     const size_t n = (size_t)bi.npix;
     if (n == 0) return PTB_OK;
     if (precision == PTB_PREC_FP32) {
@@ -505,8 +505,8 @@ extern "C" size_t ptb_trace_paths_workspace(const ptb_render_params *p, int32_t 
     return p->precision == PTB_PREC_FP64 ? queue_bytes<double>(cap, p->bounces) : queue_bytes<float>(cap, p->bounces);
 }
 
-extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
-                               float *d_accum, const ptb_path_records *records, void *stream) {
+static int trace_paths_impl(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
+                            float *d_accum, const ptb_path_records *records, const int32_t *d_sample_offset, void *stream) {
     int rc;
     if ((rc = check_scene(s, stream))) return rc;
     if (!p || (rc = check_pixels(&p->px))) return rc ? rc : PTB_ERR_ARG;
@@ -544,7 +544,7 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         PTB_LAUNCHED();
     }
     BatchInfo bi;
-    bi.pm = make_pixel_map(&p->px); bi.npix = npix; bi.seed = p->seed; bi.bounce = 0;
+    bi.pm = make_pixel_map(&p->px); bi.npix = npix; bi.seed = p->seed; bi.bounce = 0; bi.s_off = d_sample_offset;
     Queues<float> q32; Queues<double> q64;
     if (f64) queue_carve<double>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q64);
     else queue_carve<float>(d_ws, ws_bytes, (size_t)npix * S, p->bounces, q32);
@@ -558,6 +558,16 @@ extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, v
         if (rc) return rc;
     }
     return PTB_OK;
+}
+
+extern "C" int ptb_trace_paths(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
+                               float *d_accum, const ptb_path_records *records, void *stream) {
+    return trace_paths_impl(s, p, d_ws, ws_bytes, d_accum, records, nullptr, stream);
+}
+extern "C" int ptb_trace_paths_at(const ptb_scene *s, const ptb_render_params *p, void *d_ws, size_t ws_bytes,
+                                  float *d_accum, const ptb_path_records *records, const int32_t *d_sample_offset, void *stream) {
+    if (!d_sample_offset) { set_error("ptb_trace_paths_at: null sample offset"); return PTB_ERR_ARG; }
+    return trace_paths_impl(s, p, d_ws, ws_bytes, d_accum, records, d_sample_offset, stream);
 }
 
 extern "C" int ptb_tonemap(const float *d_accum, int32_t width, int32_t height, uint8_t *d_rgb, void *d_ws, void *stream) {

@@ -113,7 +113,7 @@ k_bounce_planes32(DScene sc, PlaneScene ps, BatchInfo bi, const float4 *__restri
             const f3 o = mk3(a.x, a.y, a.z), d = mk3(b.x, b.y, b.z), n = mk3(sn.x, sn.y, sn.z);
             const float k = a.w;
             const f3 P = mk3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
-            const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
+            const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = bi.sample_index(s_local);
             // ---- next-event estimation: 3 light samples, occlusion, colour (main.py:23-73, 142-145)
             float4 ld[3];
             light_samples32(sc, bi.seed, r, sample, (uint32_t)bi.bounce, P, ld);

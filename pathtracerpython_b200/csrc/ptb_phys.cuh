@@ -100,7 +100,7 @@ k_shade_phys32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const flo
         const bool has_nee = surface && (m.kd + m.ks) > 0.f;
         int s_local, p;
         fast_divmod(id, bi.npix, inv_npix, s_local, p);
-        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
+        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = bi.sample_index(s_local);
         const float cosi = -dot(d, n);
         const f3 mirror = mk3(fmaf(2.0f * cosi, n.x, d.x), fmaf(2.0f * cosi, n.y, d.y), fmaf(2.0f * cosi, n.z, d.z));
 

@@ -21,6 +21,11 @@ struct BatchInfo {
     int s_first;     // absolute index of the batch's first sample
     int bounce;
     uint32_t seed;
+    const int *s_off;   // device word added to every sample index (ptb_trace_paths_at: a captured CUDA graph renders the NEXT
+                        // samples at every replay without a new launch sequence), or null
+    __device__ __forceinline__ uint32_t sample_index(int s_local) const {
+        return (uint32_t)(s_first + s_local) + (s_off ? (uint32_t)__ldg(s_off) : 0u);
+    }
 };
 
 // ---------------------------------------------------------------- camera rays
@@ -225,7 +230,7 @@ k_shade32(DScene sc, BatchInfo bi, const float4 *__restrict__ qo, const float4 *
         const f3 P = mk3(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
         int s_local, p;
         fast_divmod(id, bi.npix, inv_npix, s_local, p);
-        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
+        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = bi.sample_index(s_local);
 
         // ---- 3 light samples (main.py:30-40)
         float4 ld[3];

@@ -79,7 +79,7 @@ k_shade64(DScene sc, BatchInfo bi, const double4 *__restrict__ qo, const double4
         const d3 P = mk3<double>(xadd(pr.x, xmul(vr.x, t)), xadd(pr.y, xmul(vr.y, t)), xadd(pr.z, xmul(vr.z, t)));
         const d3 nrm = ld3(sc.normals64 + 3 * (size_t)tri);
         const int s_local = id / bi.npix, p = id - s_local * bi.npix;
-        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = (uint32_t)(bi.s_first + s_local);
+        const uint32_t r = (uint32_t)bi.pm.ray_index(p), sample = bi.sample_index(s_local);
 
         for (int s = 0; s < 3; ++s) {
             const uint4 w = rng4(bi.seed, r, sample, (uint32_t)bi.bounce, (uint32_t)s);

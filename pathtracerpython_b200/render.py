@@ -345,3 +345,61 @@ def render(scene, n_rays=1, n_bounces=1, seed=None, width=None, height=None, dev
         return im
     finally:
         r.close()
+
+
+class ProgressiveFrame:
+    """Progressive rendering of one frame as a CUDA graph (ptb_trace_paths_at): the launch sequence of `n_rays` samples per
+    pixel - camera rays, the per-bounce kernels, the batch reduce, the tone map - is captured once; every `step()` replays it
+    with the sample offset, a device word the graph itself advances, `n_rays` further on.  After k steps `accum` holds the same
+    sums, bit for bit, as one `trace_paths(k * n_rays, ..., samples_per_batch=n_rays)`.  For frames that are launch-bound
+    (the reference's shipped 40 x 40 scene: 0.17 ms of launches for 0.03 ms of kernels) a replay costs one graph launch."""
+
+    def __init__(self, renderer, n_rays, n_bounces, seed=0, width=None, height=None, tonemap=True, flags=0):
+        torch = renderer.torch
+        self.r, self.n_rays = renderer, int(n_rays)
+        L = _lib.lib()
+        p = _lib.RenderParams()
+        p.px, self._keep = renderer.pixels(width, height)
+        self.width, self.height = int(p.px.width), int(p.px.height)
+        npix = renderer.pixel_count(p.px)
+        p.sample_begin, p.sample_end = 0, self.n_rays
+        p.bounces, p.seed, p.precision, p.flags = int(n_bounces), int(seed) & 0xFFFFFFFF, _lib.PREC_FP32, int(flags)
+        p.samples_per_batch = self.n_rays
+        self._p = p
+        dev = renderer.device
+        self.accum = torch.zeros((npix, 4), dtype=torch.float32, device=dev)
+        self.offset = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.rgb = torch.empty((self.height, self.width, 3), dtype=torch.uint8, device=dev) if tonemap else None
+        self._ws_bytes = int(L.ptb_trace_paths_workspace(C.byref(p), self.n_rays))
+        self._ws = torch.empty(self._ws_bytes, dtype=torch.uint8, device=dev)
+        self._ws_tm = torch.empty(256, dtype=torch.uint8, device=dev)
+        self.steps = 0
+        with torch.cuda.device(dev):
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):           # once outside the capture: module loading, kernel attributes
+                self._launch()
+            side.synchronize()
+            self.accum.zero_(); self.offset.zero_()
+            torch.cuda.current_stream(dev).synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self._launch()
+
+    def _launch(self):
+        torch, r, L = self.r.torch, self.r, _lib.lib()
+        st = C.c_void_p(torch.cuda.current_stream(r.device).cuda_stream)
+        _lib.check(L.ptb_trace_paths_at(r._handle, C.byref(self._p), self._ws.data_ptr(), self._ws_bytes, self.accum.data_ptr(), None,
+                                        self.offset.data_ptr(), st), "ptb_trace_paths_at")
+        self.offset.add_(self.n_rays)
+        if self.rgb is not None:
+            _lib.check(L.ptb_tonemap(self.accum.data_ptr(), self.width, self.height, self.rgb.data_ptr(), self._ws_tm.data_ptr(), st), "ptb_tonemap")
+
+    def step(self):
+        """n_rays more samples per pixel -> (accum, rgb)."""
+        self.graph.replay()
+        self.steps += 1
+        return self.accum, self.rgb
+
+    def reset(self):
+        self.accum.zero_(); self.offset.zero_(); self.steps = 0
