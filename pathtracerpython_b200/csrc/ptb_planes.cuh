@@ -26,12 +26,40 @@ struct PlaneScene {    // device pointer, small; staged into shared memory by ev
 };
 
 __host__ __device__ inline size_t plane_smem_bytes(int n_planes) { return (size_t)n_planes * sizeof(PlaneRec) + 16; }
+// The plane list of a small scene (<= 48 KB) is staged into shared memory once per persistent block: ONE TMA bulk copy
+// (cp.async.bulk.shared::cluster.global, SASS UBLKCP) issued by thread 0, its completion counted in bytes on an mbarrier
+// that lives in the 16 spare bytes behind the records (plane_smem_bytes); every thread waits on phase 0 of the barrier.
+// PTB_PLANES_TMA=0: the plain coalesced copy of round 1.
+#ifndef PTB_PLANES_TMA
+#define PTB_PLANES_TMA 1
+#endif
 __device__ __forceinline__ const PlaneRec *stage_planes(unsigned char *smem, const PlaneScene &ps) {
+#if PTB_PLANES_TMA
+    const unsigned bytes = (unsigned)ps.n_planes * (unsigned)sizeof(PlaneRec);          // a multiple of 32
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smem), mb = dst + bytes;
+    if (bytes) {
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst), "l"(ps.planes), "r"(bytes), "r"(mb) : "memory");
+        }
+        __syncthreads();                    // the barrier is initialised before anybody polls it
+        unsigned done = 0;
+        do {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(mb) : "memory");
+        } while (!done);
+    }
+    return reinterpret_cast<const PlaneRec *>(smem);
+#else
     const float4 *a = reinterpret_cast<const float4 *>(ps.planes);
     float4 *da = reinterpret_cast<float4 *>(smem);
     for (int i = threadIdx.x; i < ps.n_planes * 6; i += blockDim.x) da[i] = __ldg(a + i);
     __syncthreads();
     return reinterpret_cast<const PlaneRec *>(smem);
+#endif
 }
 
 // Parallelogram pair: with (u, v) the barycentrics of triangle A, P = a1 + (u+v)(a2-a1) + v(a4-a1), so P is in
