@@ -195,7 +195,6 @@ int ptb_trace_closest(const ptb_scene *scene, const void *d_rays, int64_t n, int
 #define PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS 131072
 int ptb_trace_closest_noalloc(const ptb_scene *scene, const void *d_rays, int64_t n, int32_t precision,
                               int32_t *d_tri, void *d_t, void *stream);
-int64_t ptb_trace_closest_noalloc_max_rays(void);
 
 /* replaces the sample loop x bounce loop of main() (main.py:186-271): for every pixel of the set and
  * every sample in [s0, s1) it ADDS the sample's radiance to d_accum[pixel_slot] (float4: r, g, b,

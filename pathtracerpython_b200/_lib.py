@@ -10,6 +10,7 @@ PREC_FP32, PREC_FP64 = 0, 1
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_LBVH = 0, 1, 2
 SCENE_ARRAYS_ON_DEVICE = 1
 FLAG_NO_FP64_RETRACE, FLAG_SEPARATE_KERNELS, FLAG_COUNT_NODES, FLAG_PHYSICAL, FLAG_NO_ROULETTE = 1, 2, 4, 8, 16
+TRACE_CLOSEST_NOALLOC_MAX_RAYS = 131072      # include/ptb.h PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS
 
 EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destroy", "ptb_scene_info",
            "ptb_trace_primary", "ptb_trace_closest", "ptb_trace_paths_workspace", "ptb_trace_paths",
@@ -17,7 +18,7 @@ EXPORTS = ["ptb_last_error", "ptb_version", "ptb_scene_create", "ptb_scene_destr
            "ptb_profile_enable", "ptb_profile_read", "ptb_fp32_peak", "ptb_trace_primary_workspace",
            "ptb_obj_parse", "ptb_obj_free", "ptb_obj_write", "ptb_bvh_export_bytes", "ptb_bvh_export", "ptb_bvh_import", "ptb_tonemap_scene", "ptb_pool_trim",
            "ptb_gather_peak", "ptb_gather_peak_smem", "ptb_kat", "ptb_scene_plane_culling",
-           "ptb_trace_closest_noalloc", "ptb_trace_closest_noalloc_max_rays", "ptb_trace_paths_at"]
+           "ptb_trace_closest_noalloc", "ptb_trace_paths_at"]
 
 
 class PtbError(RuntimeError):
@@ -81,7 +82,6 @@ def lib():
                                         C.c_void_p, C.c_size_t, C.c_void_p]
         L.ptb_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptb_trace_closest_noalloc.argtypes = L.ptb_trace_closest.argtypes
-        L.ptb_trace_closest_noalloc_max_rays.restype = C.c_int64
         L.ptb_trace_paths_workspace.argtypes = [C.POINTER(RenderParams), C.c_int32]
         L.ptb_trace_paths.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_size_t, C.c_void_p,
                                       C.POINTER(PathRecords), C.c_void_p]

@@ -878,8 +878,6 @@ static int noalloc_scratch(char **out) {
 }
 }  // namespace ptb
 
-extern "C" int64_t ptb_trace_closest_noalloc_max_rays(void) { return PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS; }
-
 extern "C" int ptb_trace_closest_noalloc(const ptb_scene *s, const void *d_rays, int64_t n, int32_t precision,
                                          int32_t *d_tri, void *d_t, void *stream) {
     int rc;

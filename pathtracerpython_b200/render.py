@@ -186,7 +186,7 @@ class Renderer:
     def trace_closest_noalloc(self, rays, tri, t, precision=_lib.PREC_FP32):
         """ptb_trace_closest_noalloc: the same query into caller-owned DEVICE tensors (`rays` [n, 6] float32 / float64
         contiguous, `tri` int32 [n], `t` like rays [n]); the library allocates nothing (its scratch is a fixed device
-        array), at most `ptb_trace_closest_noalloc_max_rays()` rays per call, calls must not overlap on the GPU."""
+        array), at most `_lib.TRACE_CLOSEST_NOALLOC_MAX_RAYS` rays per call, calls must not overlap on the GPU."""
         n = rays.shape[0]
         with self.torch.cuda.device(self.device):
             _lib.check(_lib.lib().ptb_trace_closest_noalloc(self._handle, rays.data_ptr(), n, precision, tri.data_ptr(),

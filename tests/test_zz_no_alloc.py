@@ -56,8 +56,8 @@ def test_noalloc_limit_and_arguments():
     import torch
     r = ptb.Renderer(ptb.CORNELL_SDL, device=0)
     L = _lib.lib()
-    cap = int(L.ptb_trace_closest_noalloc_max_rays())
-    assert cap == 131072
+    cap = _lib.TRACE_CLOSEST_NOALLOC_MAX_RAYS
+    assert cap == 131072                  # include/ptb.h PTB_TRACE_CLOSEST_NOALLOC_MAX_RAYS
     n = cap + 1
     rays = torch.zeros((n, 6), dtype=torch.float32, device=r.device)
     rays[:, 5] = 1.0
