@@ -107,6 +107,26 @@ static void l2_window(cudaStream_t st, const void *base, size_t bytes) {
     if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
 }
 
+// Blocks per SM in the grid of the fused per-bounce kernel (4 are resident).  The tiles of a launch are dealt out to the blocks
+// with a fixed stride, so a block's share of slow tiles is luck: with more, shorter blocks the SMs that finish early pick up
+// new blocks, and the blocks that run at the same time stay on neighbouring tiles of the queues (measured, Msamples/s: 4 -> 2 843,
+// 8 -> 3 013, 16 -> 3 110, 32 -> 3 172, 128 -> 3 198, 512 -> 3 185, one tile per block 2 890; PTB_FUSED_GRID=n overrides).
+#ifndef PTB_FUSED2_GRID
+#define PTB_FUSED2_GRID 128
+#endif
+static int fused_grid_blocks_per_sm() {
+    static const int v = [] { const char *e = getenv("PTB_FUSED_GRID"); const int n = e ? atoi(e) : 0; return n > 0 ? n : PTB_FUSED2_GRID; }();
+    return v;
+}
+
+#ifndef PTB_SHADE_GRID
+#define PTB_SHADE_GRID 8
+#endif
+static int shade_grid_blocks_per_sm() {     // k_shade32 / k_nee_finish32 of the LBVH pipeline (PTB_SHADE_GRID_ENV=n overrides)
+    static const int v = [] { const char *e = getenv("PTB_SHADE_GRID_ENV"); const int n = e ? atoi(e) : 0; return n > 0 ? n : PTB_SHADE_GRID; }();
+    return v;
+}
+
 // closest-hit over queue `in` for the brute-force scene
 static int launch_closest32(const ptb_scene *s, Queues<float> &q, int in, const unsigned *d_count, size_t upper,
                             bool track, float *hit_t, int *hit_tri, cudaStream_t st, const unsigned *order = nullptr,
@@ -290,7 +310,7 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             bi.bounce = b;
             const int last = b == p->bounces - 1;
             ProfScope ps_(PK_BOUNCE, st);
-            const int grid_b = grid_for(N, PTB_SHADE_THREADS, 8);
+            const int grid_b = grid_for(N, PTB_SHADE_THREADS, fused_grid_blocks_per_sm());
             if (s->fused_x2) {      // packed FP32 (ptb_fused2.cuh): same results bit for bit, fewer issue slots
                 const float4 *qi = b == 0 ? q.qo[0] : q.qo[in], *di = b == 0 ? q.qd[0] : q.qd[in];
                 const unsigned *cin = q.count + b;
@@ -333,7 +353,7 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             PTB_LAUNCHED();
         }
         { ProfScope ps_(PK_SHADE, st);
-        k_shade32<<<grid_for(N, PTB_SHADE_THREADS, 8), PTB_SHADE_THREADS, 0, st>>>(
+        k_shade32<<<grid_for(N, PTB_SHADE_THREADS, shade_grid_blocks_per_sm()), PTB_SHADE_THREADS, 0, st>>>(
             d, bi, q.qo[in], q.qd[in], q.hit_t, q.hit_tri, q.count + b, q.count + b + 1, q.qo[out], q.qd[out],
             q.sh_p, q.sh_d, q.sh_aux, q.L, q.cap, rec, sorting ? q.sort.keys[0] : nullptr, (share && b == 0) ? 1 : 0, origin_pid);
         }
@@ -365,7 +385,7 @@ static int run_batch32(const ptb_scene *s, const ptb_render_params *p, Queues<fl
             else
                 k_shadow_bvh32_dyn<false><<<grid_for(3 * N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, PTB_DYN_SMEM, st>>>(d, q.sh_p, q.sh_d, q.count + b + 1, q.sh_res, q.cap, work, order);
             PTB_LAUNCHED();
-            k_nee_finish32<<<grid_for(N, 256, 8), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
+            k_nee_finish32<<<grid_for(N, 256, shade_grid_blocks_per_sm()), 256, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.sh_res, q.count + b + 1, q.L, q.cap, b, rec);
         } else if (d.accel == PTB_ACCEL_LBVH) {
             if (q.count_nodes)
                 k_shadow_bvh32<true><<<grid_for(N, PTB_BVH_THREADS, 12), PTB_BVH_THREADS, 0, st>>>(d, q.sh_p, q.sh_d, q.sh_aux, q.count + b + 1, q.L, q.cap, b, rec);

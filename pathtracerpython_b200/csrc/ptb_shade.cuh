@@ -12,7 +12,9 @@
 
 namespace ptb {
 
+#ifndef PTB_SHADE_THREADS
 #define PTB_SHADE_THREADS 256
+#endif
 
 struct BatchInfo {
     PixelMap pm;
