@@ -212,20 +212,45 @@ def run_reference(a):
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons of one GPU, sampled every 0.2 s DURING the timed region.  In-process NVML queries
+    (nvidia_ml_py: the library nvidia-smi itself is a client of) - spawning nvidia-smi five times a second was measured to
+    stall the GPU's queue for milliseconds at a time, which a 4 ms frame cannot absorb; nvidia-smi stays as the fallback."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nvml, self.handle = None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self._nvml_row()
+        except Exception:
+            self.nvml = None
+
+    def _nvml_row(self):
+        N, h = self.nvml, self.handle
+        sm, mx = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM), N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+        try:
+            r = N.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            r = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        bits = (N.nvmlClocksThrottleReasonHwSlowdown, N.nvmlClocksThrottleReasonHwThermalSlowdown,
+                N.nvmlClocksThrottleReasonSwThermalSlowdown, N.nvmlClocksThrottleReasonSwPowerCap)
+        return [str(sm), str(mx)] + ["Active" if (r & b) else "Not Active" for b in bits]
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                if self.nvml is not None:
+                    self.rows.append(self._nvml_row())
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                         capture_output=True, text=True, timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
             time.sleep(0.2)
@@ -233,13 +258,13 @@ class ClockSampler(threading.Thread):
     def summary(self):
         self.stop_flag = True
         if self.is_alive():
-            self.join(timeout=10)      # an nvidia-smi query still in flight holds a driver lock: keep it out of the e2e leg
+            self.join(timeout=10)      # a query still in flight holds a driver lock: keep it out of the e2e leg
         sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None,
                 "sm_max_mhz": max((int(r[1]) for r in self.rows if r[1].isdigit()), default=None),
-                "reasons": reasons, "samples": len(self.rows)}
+                "reasons": reasons, "samples": len(self.rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------ our arm
@@ -301,7 +326,7 @@ def traffic_table():
     return None, None
 
 
-def measure(ctx, spec, steps, warmup, e2e_replicated=False):
+def measure(ctx, spec, steps, warmup, e2e_replicated=False, min_region_ms=0.0):
     """One workload on this rank's share: resident-scene value, end-to-end value, ray rates, roofline of the dominant
     kernel, clocks.  Every rank calls it; the dict is meaningful on rank 0."""
     import numpy as np
@@ -321,6 +346,11 @@ def measure(ctx, spec, steps, warmup, e2e_replicated=False):
     for _ in range(warmup):
         step(r)
     torch.cuda.synchronize()
+    if min_region_ms > 0:
+        # secondary workloads with millisecond frames: time enough frames for the region to outlast one scheduling hiccup
+        # or one nvidia-smi query of the clock sampler (a 512^2 x 64 spp frame is 3.8 ms; the headline keeps EXACTLY `steps`)
+        est = ctx.timed(lambda: step(r), 1)
+        steps = int(max(steps, min(2000, -(-min_region_ms // max(est, 1e-3)))))
     r.counters(reset=True)
     _lib.profile_enable(True)
     _lib.profile_read()
@@ -529,7 +559,7 @@ def run_ours(a):
             specs = [Spec(3840, 2160, 64, 5, tess=559, shard="sample", label=f"C5 strong: 64 spp in total, sample ranges over {world} GPUs"),
                      Spec(3840, 2160, 8 * world, 5, tess=559, shard="sample", label=f"C5 weak: 8 spp per GPU ({8 * world} in total)")]
         for sp in specs:
-            e2, r2, _ = measure(ctx, sp, ks, kw, e2e_replicated=True)
+            e2, r2, _ = measure(ctx, sp, ks, kw, e2e_replicated=True, min_region_ms=300.0)
             if e2 is not None:
                 if "weak" in (sp.label or ""):
                     e2["scaling"] = "weak"
