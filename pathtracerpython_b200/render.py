@@ -239,6 +239,16 @@ class Renderer:
             if samples_per_batch:
                 spb = min(spb, samples_per_batch)
             ws_bytes = L.ptb_trace_paths_workspace(C.byref(p), spb)
+            if held is not None and ws_bytes > held.numel():
+                # Free memory moves by a few MB between calls (a scene created, an image buffer), and one sample per batch
+                # more than last time would throw a workspace of tens of GB away and allocate a larger one - 20 ms of
+                # cudaFree / cudaMalloc.  If what is held takes at least 3/4
+                # of the batch just computed, the batch is cut to what is held.
+                fit = int(min(spb, held.numel() // max(one, 1)))
+                while fit > 0 and L.ptb_trace_paths_workspace(C.byref(p), fit) > held.numel():
+                    fit -= 1
+                if 4 * fit >= 3 * spb:
+                    spb, ws_bytes = fit, L.ptb_trace_paths_workspace(C.byref(p), fit)
         ws = self.workspace(ws_bytes)
         with torch.cuda.device(self.device):
             # the size asked for, not the (shared, possibly larger) tensor's: a caller-imposed budget stays a budget
